@@ -1,0 +1,45 @@
+/*
+ * rtow_b200_scenes.h -- C entry points over the host-side scene API (include/rtow/scene_api.h,
+ * scenes.h, extra_scenes.h) for callers that are not C++ (the pytest harness, bench.py, the CLI).
+ *
+ * They run the scene builders that mirror the reference's scenes.h:29,122,220,355 (plus the two
+ * BASELINE.json scenes the reference lacks) and flatten the result; the returned rtow_scene_desc
+ * is what rtow_scene_create() takes.  No rendering or intersection happens here.
+ */
+#ifndef RTOW_B200_SCENES_H
+#define RTOW_B200_SCENES_H
+
+#include "rtow_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rtow_host_scene rtow_host_scene;
+
+/* name: random | random_ned | cornell | cornell_ned | cornell_smoke_ned | bvh_stress.
+ * seed: seeds the builders' engine (the reference time-seeds it, main.cpp:82-88).
+ * n: sphere count for bvh_stress.  wrap != 0 adds main()'s root Translate (main.cpp:132,136). */
+int rtow_host_scene_build(const char *name, uint64_t seed, int n, int wrap, rtow_host_scene **out);
+const rtow_scene_desc *rtow_host_scene_desc(const rtow_host_scene *scene);
+void rtow_host_scene_free(rtow_host_scene *scene);
+
+/* Pixels (RGB8, copied) the next builders' image loads return instead of reading
+ * ./input_images/<name> (scenes.h:47,140); nx = 0 clears the override. */
+int rtow_host_set_image(const uint8_t *rgb, int32_t nx, int32_t ny);
+
+/* Camera(lookFrom, lookAt, up, vFoV, aspect, aperture, focusDistance, t0, t1) of camera.h:13
+ * -> the POD frame of camera.h:315-342. */
+int rtow_host_camera(const float look_from[3], const float look_at[3], const float up[3], float vfov,
+                     float aspect, float aperture, float focus_distance, float t0, float t1,
+                     rtow_camera *out);
+
+/* Headless image writers (replace winDIBbitmap.cpp / the GDI window).
+ * rgb = W*H*3 linear floats, row 0 = top.  PPM applies the reference tone curve main.cpp:955-970. */
+int rtow_write_ppm(const char *path, const float *rgb_linear, int32_t width, int32_t height);
+int rtow_write_pfm(const char *path, const float *rgb_linear, int32_t width, int32_t height);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
