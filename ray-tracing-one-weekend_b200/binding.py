@@ -1,0 +1,211 @@
+"""ctypes binding of include/rtow_b200.h and include/rtow_b200_scenes.h.
+
+Mirrors the reference-facing calls one to one; every function returns through the C status
+code and raises RtowError with rtow_last_error() on failure.  There is no Python-side
+computation and no fallback path.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _abi as abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class RtowError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"rtow error {code}: {msg}")
+        self.code = code
+
+
+def lib_path():
+    return os.path.join(_HERE, "csrc", "librtow_b200.so")
+
+
+def lib():
+    """The CUDA library.  Missing library = hard error (there is no CPU fallback)."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = lib_path()
+    if not os.path.exists(path):
+        raise RuntimeError(
+            f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). There is no CPU fallback."
+        )
+    L = C.CDLL(path)
+    vp, i32, u64, f32 = C.c_void_p, C.c_int32, C.c_uint64, C.c_float
+    P = C.POINTER
+    sig = {
+        "rtow_device_count": (C.c_int, []),
+        "rtow_scene_create": (C.c_int, [P(abi.SceneDesc), C.c_int, P(vp)]),
+        "rtow_scene_destroy": (None, [vp]),
+        "rtow_trace_rays": (C.c_int, [vp, vp, u64, vp, C.c_int, u64, P(abi.Stats)]),
+        "rtow_trace_rays_device": (C.c_int, [vp, vp, u64, vp, C.c_int, u64, vp]),
+        "rtow_render": (C.c_int, [vp, P(abi.Camera), P(abi.RenderParams), vp, vp, P(abi.Stats)]),
+        "rtow_render_accumulate_device": (C.c_int, [vp, P(abi.Camera), P(abi.RenderParams), vp, vp]),
+        "rtow_stream_stats": (C.c_int, [vp, vp, P(abi.Stats)]),
+        "rtow_resolve_device": (C.c_int, [vp, vp, i32, i32, i32, vp, vp, vp]),
+        "rtow_trace_counters": (C.c_int, [vp, vp, u64, C.c_int, P(C.c_double), P(C.c_double)]),
+        "rtow_last_error": (C.c_char_p, []),
+        "rtow_build_info": (C.c_char_p, []),
+        "rtow_host_scene_build": (C.c_int, [C.c_char_p, u64, C.c_int, C.c_int, P(vp)]),
+        "rtow_host_scene_desc": (P(abi.SceneDesc), [vp]),
+        "rtow_host_scene_free": (None, [vp]),
+        "rtow_host_set_image": (C.c_int, [vp, i32, i32]),
+        "rtow_host_camera": (C.c_int, [P(f32 * 3), P(f32 * 3), P(f32 * 3), f32, f32, f32, f32, f32, f32, P(abi.Camera)]),
+        "rtow_write_ppm": (C.c_int, [C.c_char_p, vp, i32, i32]),
+        "rtow_write_pfm": (C.c_int, [C.c_char_p, vp, i32, i32]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)   # AttributeError here = the library does not export what the header declares
+        fn.restype, fn.argtypes = res, args
+    _LIB = L
+    return L
+
+
+EXPORTED_SYMBOLS = [
+    "rtow_device_count", "rtow_scene_create", "rtow_scene_destroy", "rtow_trace_rays", "rtow_trace_rays_device",
+    "rtow_render", "rtow_render_accumulate_device", "rtow_stream_stats", "rtow_resolve_device", "rtow_trace_counters",
+    "rtow_last_error", "rtow_build_info", "rtow_host_scene_build", "rtow_host_scene_desc", "rtow_host_scene_free",
+    "rtow_host_set_image", "rtow_host_camera", "rtow_write_ppm", "rtow_write_pfm",
+]
+
+
+def _check(code):
+    if code != abi.OK:
+        raise RtowError(code, lib().rtow_last_error().decode(errors="replace"))
+
+
+def _vec3(v):
+    return (C.c_float * 3)(*[float(x) for x in v])
+
+
+def make_camera(look_from, look_at, up, vfov, aspect, aperture, focus, t0=0.0, t1=1.0):
+    """Camera(lookFrom, lookAt, up, vFoV, aspect, aperture, focusDistance, t0, t1) -- camera.h:13."""
+    cam = abi.Camera()
+    _check(lib().rtow_host_camera(C.byref(_vec3(look_from)), C.byref(_vec3(look_at)), C.byref(_vec3(up)),
+                                  vfov, aspect, aperture, focus, t0, t1, C.byref(cam)))
+    return cam
+
+
+def main_camera(width, height):
+    """The camera main() builds: main.cpp:111-125."""
+    return make_camera((0, 0, 0), (1, 0, 0), (0, 0, -1), 60.0, float(width) / float(height), 2.0, 1000.0, 0.0, 1.0)
+
+
+class HostScene:
+    """A scene built by the host-side scene API (mirrors scenes.h) and flattened."""
+
+    def __init__(self, name, seed=12345, n=0, wrap=True, image=None):
+        L = lib()
+        if image is not None:
+            img = np.ascontiguousarray(image, dtype=np.uint8)
+            assert img.ndim == 3 and img.shape[2] == 3
+            _check(L.rtow_host_set_image(img.ctypes.data, img.shape[1], img.shape[0]))
+        else:
+            _check(L.rtow_host_set_image(None, 0, 0))
+        h = C.c_void_p()
+        try:
+            _check(L.rtow_host_scene_build(name.encode(), seed, n, 1 if wrap else 0, C.byref(h)))
+        finally:
+            L.rtow_host_set_image(None, 0, 0)
+        self._h = h
+        self.name = name
+
+    @property
+    def desc(self):
+        return lib().rtow_host_scene_desc(self._h).contents
+
+    def arrays(self):
+        return abi.desc_arrays(self.desc)
+
+    def close(self):
+        if self._h:
+            lib().rtow_host_scene_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DeviceScene:
+    """rtow_scene*: device copies of a flattened scene + the traversal structures."""
+
+    def __init__(self, desc, device=0):
+        L = lib()
+        h = C.c_void_p()
+        _check(L.rtow_scene_create(C.byref(desc), device, C.byref(h)))
+        self._h = h
+        self.device = device
+
+    def close(self):
+        if self._h:
+            lib().rtow_scene_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- world->hit() ---------------------------------------------------------------------
+    def trace(self, rays, traverse=abi.TRAVERSE_AUTO, seed=0):
+        rays = np.ascontiguousarray(rays, dtype=abi.ray_dtype)
+        hits = np.zeros(len(rays), dtype=abi.hit_dtype)
+        st = abi.Stats()
+        _check(lib().rtow_trace_rays(self._h, rays.ctypes.data, len(rays), hits.ctypes.data, traverse, seed, C.byref(st)))
+        return hits, st
+
+    def trace_device(self, d_rays_ptr, n, d_hits_ptr, traverse=abi.TRAVERSE_AUTO, seed=0, stream=None):
+        _check(lib().rtow_trace_rays_device(self._h, d_rays_ptr, n, d_hits_ptr, traverse, seed, stream))
+
+    def trace_counters(self, rays, traverse=abi.TRAVERSE_AUTO):
+        rays = np.ascontiguousarray(rays, dtype=abi.ray_dtype)
+        nv, pt = C.c_double(), C.c_double()
+        _check(lib().rtow_trace_counters(self._h, rays.ctypes.data, len(rays), traverse, C.byref(nv), C.byref(pt)))
+        return nv.value, pt.value
+
+    # -- the pixel loop -------------------------------------------------------------------
+    def render(self, cam, params, want_bgra=False):
+        W, H = params.width, params.height
+        rgb = np.zeros((H, W, 3), dtype=np.float32)
+        bgra = np.zeros((H, W, 4), dtype=np.uint8) if want_bgra else None
+        st = abi.Stats()
+        _check(lib().rtow_render(self._h, C.byref(cam), C.byref(params), rgb.ctypes.data,
+                                 bgra.ctypes.data if want_bgra else None, C.byref(st)))
+        return (rgb, bgra, st) if want_bgra else (rgb, st)
+
+    def render_into(self, cam, params, rgb_out, bgra_out=None):
+        """Host buffers supplied by the caller (pinned buffers in bench.py's e2e leg)."""
+        st = abi.Stats()
+        _check(lib().rtow_render(self._h, C.byref(cam), C.byref(params), rgb_out, bgra_out, C.byref(st)))
+        return st
+
+    def accumulate_device(self, cam, params, d_accum_ptr, stream=None):
+        _check(lib().rtow_render_accumulate_device(self._h, C.byref(cam), C.byref(params), d_accum_ptr, stream))
+
+    def stream_stats(self, stream=None):
+        st = abi.Stats()
+        _check(lib().rtow_stream_stats(self._h, stream, C.byref(st)))
+        return st
+
+    def resolve_device(self, d_accum_ptr, width, height, spp, d_rgb_ptr=None, d_bgra_ptr=None, stream=None):
+        _check(lib().rtow_resolve_device(self._h, d_accum_ptr, width, height, spp, d_rgb_ptr, d_bgra_ptr, stream))
+
+
+def write_ppm(path, rgb):
+    rgb = np.ascontiguousarray(rgb, dtype=np.float32)
+    _check(lib().rtow_write_ppm(str(path).encode(), rgb.ctypes.data, rgb.shape[1], rgb.shape[0]))
+
+
+def write_pfm(path, rgb):
+    rgb = np.ascontiguousarray(rgb, dtype=np.float32)
+    _check(lib().rtow_write_pfm(str(path).encode(), rgb.ctypes.data, rgb.shape[1], rgb.shape[0]))
