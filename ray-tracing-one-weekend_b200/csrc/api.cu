@@ -1,0 +1,499 @@
+// api.cu -- the C ABI of include/rtow_b200.h: scene upload, trace, render, resolve.
+// Host-side glue only; every intersection / shading instruction lives in kernels.cu.
+// There is no CPU path behind these symbols: without a CUDA device they return RTOW_ERR_NO_DEVICE.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "errors.h"
+#include "fast_bvh.h"
+#include "rt_kernels.cuh"
+
+using namespace rtow;
+
+struct rtow_scene {
+    int device = 0;
+    DScene d;
+    std::vector<void *> allocs;
+    unsigned long long *d_counters = nullptr;   // rays, paths, node visits, prim tests
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool pending = false;                       // an accumulate call is in flight on some stream
+    uint32_t pending_launches = 0;
+    // work buffers of the host-buffer entry points (grown on demand)
+    void *d_rays = nullptr, *d_hits = nullptr; size_t ray_cap = 0;
+    float *d_accum = nullptr, *d_rgb = nullptr; uint8_t *d_bgra = nullptr; size_t img_cap = 0;
+    cudaStream_t stream = nullptr;
+    bool has_fast = false;
+};
+
+namespace {
+
+#define CUDA_TRY(expr)                                                                                         \
+    do {                                                                                                       \
+        cudaError_t _e = (expr);                                                                               \
+        if (_e != cudaSuccess)                                                                                 \
+            return set_error(_e == cudaErrorMemoryAllocation ? RTOW_ERR_OOM : RTOW_ERR_CUDA,                  \
+                             std::string(#expr) + ": " + cudaGetErrorString(_e));                              \
+    } while (0)
+
+template <class T>
+int upload(rtow_scene *s, const T *host, size_t count, const T **dev) {
+    *dev = nullptr;
+    if (count == 0) return RTOW_OK;
+    void *p = nullptr;
+    CUDA_TRY(cudaMalloc(&p, count * sizeof(T)));
+    s->allocs.push_back(p);
+    CUDA_TRY(cudaMemcpy(p, host, count * sizeof(T), cudaMemcpyHostToDevice));
+    *dev = (const T *)p;
+    return RTOW_OK;
+}
+
+int validate(const rtow_scene_desc *d) {
+    auto bad = [](const std::string &m) { return set_error(RTOW_ERR_INVALID_ARG, "rtow_scene_create: " + m); };
+    if (d->abi_version != RTOW_ABI_VERSION) return bad("abi_version mismatch");
+    if (d->n_xforms < 0 || d->n_prims < 0 || d->n_objects < 0 || d->n_nodes < 0 || d->n_materials < 0 || d->n_textures < 0 || d->n_images < 0)
+        return bad("negative count");
+    if ((d->n_xforms && !d->xforms) || (d->n_prims && !d->prims) || (d->n_objects && !d->objects) || (d->n_nodes && !d->nodes) ||
+        (d->n_materials && !d->materials) || (d->n_textures && !d->textures) || (d->n_images && !d->images))
+        return bad("null array with non-zero count");
+    if (d->top_kind != RTOW_TOP_LIST && d->top_kind != RTOW_TOP_BVH) return bad("unknown top_kind");
+    auto chain_ok = [&](int b, int n) { return n >= 0 && b >= 0 && (long long)b + n <= d->n_xforms; };
+    if (!chain_ok(d->root_xform_begin, d->root_xform_count)) return bad("root xform chain out of range");
+    for (int i = 0; i < d->n_xforms; ++i)
+        if (d->xforms[i].type < RTOW_XF_TRANSLATE || d->xforms[i].type > RTOW_XF_FLIP) return bad("unknown xform type");
+    for (int i = 0; i < d->n_textures; ++i) {
+        const rtow_texture &t = d->textures[i];
+        if (t.type < RTOW_TEX_CONSTANT || t.type > RTOW_TEX_IMAGE) return set_error(RTOW_ERR_UNSUPPORTED, "unknown texture type");
+        // children precede their parent (flatten.h numbers them first): no cycles possible
+        if (t.type == RTOW_TEX_CHECKER && (t.a < 0 || t.a >= i || t.b < 0 || t.b >= i)) return bad("checker child texture id out of range");
+        if (t.type == RTOW_TEX_IMAGE && (t.a < 0 || t.a >= d->n_images)) return bad("image id out of range");
+        if (t.type == RTOW_TEX_NOISE && !d->perlin) return bad("NOISE texture without perlin tables");
+    }
+    for (int i = 0; i < d->n_images; ++i)
+        if (!d->images[i].data || d->images[i].nx <= 0 || d->images[i].ny <= 0) return bad("empty image");
+    for (int i = 0; i < d->n_materials; ++i) {
+        const rtow_material &m = d->materials[i];
+        if (m.type < RTOW_MAT_LAMBERTIAN || m.type > RTOW_MAT_ISOTROPIC) return set_error(RTOW_ERR_UNSUPPORTED, "unknown material type");
+        bool textured = m.type == RTOW_MAT_LAMBERTIAN || m.type == RTOW_MAT_DIFFUSE_LIGHT || m.type == RTOW_MAT_ISOTROPIC;
+        if (textured && (m.tex_id < 0 || m.tex_id >= d->n_textures)) return bad("material texture id out of range");
+    }
+    for (int i = 0; i < d->n_prims; ++i) {
+        const rtow_prim &p = d->prims[i];
+        if (p.type < RTOW_PRIM_SPHERE || p.type > RTOW_PRIM_MEDIUM) return set_error(RTOW_ERR_UNSUPPORTED, "unknown primitive type");
+        if (p.mat_id < 0 || p.mat_id >= d->n_materials) return bad("primitive material id out of range");
+        if (!chain_ok(p.xform_begin, p.xform_count)) return bad("primitive xform chain out of range");
+        if (p.type == RTOW_PRIM_MEDIUM) {
+            if (p.child_count < 0 || p.child_begin < 0 || (long long)p.child_begin + p.child_count > d->n_prims) return bad("medium boundary out of range");
+            for (int c = p.child_begin; c < p.child_begin + p.child_count; ++c)
+                if (d->prims[c].type == RTOW_PRIM_MEDIUM) return set_error(RTOW_ERR_UNSUPPORTED, "medium nested in a medium boundary");
+        }
+    }
+    for (int i = 0; i < d->n_objects; ++i) {
+        const rtow_object &o = d->objects[i];
+        if (o.prim_count < 0 || o.prim_begin < 0 || (long long)o.prim_begin + o.prim_count > d->n_prims) return bad("object run out of range");
+    }
+    if (d->top_kind == RTOW_TOP_BVH) {
+        if (d->root_node < 0 || d->root_node >= d->n_nodes) return bad("root_node out of range");
+        for (int i = 0; i < d->n_nodes; ++i) {
+            const rtow_bvh_node &n = d->nodes[i];
+            for (int c : {n.left, n.right}) {
+                if (c >= 0 ? c >= d->n_nodes : ~c >= d->n_objects) return bad("bvh child out of range");
+                if (c >= 0 && c <= i) return bad("bvh nodes must be numbered parent-first");   // also rules out cycles
+            }
+        }
+    }
+    return RTOW_OK;
+}
+
+struct Entry { float a[4]; float b[4]; };
+inline float i2f(int32_t v) { float f; std::memcpy(&f, &v, 4); return f; }
+
+// Threaded pre-order form of the reference tree (rt_device.cuh).  Iterative to survive deep trees.
+void build_entries(const rtow_scene_desc *d, const std::vector<int4> &objs, std::vector<Entry> &out) {
+    struct Frame { int node; int stage; int entry; };
+    std::vector<Frame> st;
+    st.push_back({d->root_node, 0, -1});
+    auto leaf = [&](int obj, int visit) {
+        Entry e; std::memset(&e, 0, sizeof e);
+        const int4 &o = objs[obj];
+        const rtow_prim *sp = o.w >= 0 ? &d->prims[o.w] : nullptr;
+        if (sp && sp->type == RTOW_PRIM_SPHERE && sp->xform_count == 0) {
+            e.a[0] = sp->f[0]; e.a[1] = sp->f[1]; e.a[2] = sp->f[2]; e.a[3] = sp->f[3];
+            e.b[0] = i2f(o.w); e.b[3] = i2f(ENTRY_SPHERE);
+        } else {
+            e.b[0] = i2f(obj); e.b[1] = i2f(visit); e.b[3] = i2f(ENTRY_OBJECT);
+        }
+        out.push_back(e);
+    };
+    while (!st.empty()) {
+        Frame &f = st.back();
+        const rtow_bvh_node &n = d->nodes[f.node];
+        if (f.stage == 0) {
+            f.entry = (int)out.size();
+            Entry e;
+            e.a[0] = n.bmin[0]; e.a[1] = n.bmin[1]; e.a[2] = n.bmin[2]; e.a[3] = 0;
+            e.b[0] = n.bmax[0]; e.b[1] = n.bmax[1]; e.b[2] = n.bmax[2]; e.b[3] = i2f(ENTRY_NODE);
+            out.push_back(e);
+            f.stage = 1;
+            if (n.left >= 0) { st.push_back({n.left, 0, -1}); continue; }
+            leaf(~n.left, 0);
+        }
+        if (f.stage == 1) {
+            f.stage = 2;
+            if (n.right == n.left) {
+                // n == 1 node: the reference evaluates the leaf twice (bvhNode.h:38-40,70-71); only a
+                // medium can answer differently the second time (fresh free-flight draw)
+                if (n.left < 0 && (objs[~n.left].z & 1)) leaf(~n.left, 1);
+            } else if (n.right >= 0) {
+                int child = n.right;
+                st.push_back({child, 0, -1});
+                continue;
+            } else {
+                leaf(~n.right, 0);
+            }
+        }
+        out[st.back().entry].a[3] = i2f((int)out.size());
+        st.pop_back();
+    }
+}
+
+bool texture_needs_uv(const rtow_scene_desc *d, int tex) {
+    const rtow_texture &t = d->textures[tex];
+    if (t.type == RTOW_TEX_IMAGE) return true;
+    if (t.type == RTOW_TEX_CHECKER) return texture_needs_uv(d, t.a) || texture_needs_uv(d, t.b);
+    return false;
+}
+
+int ensure_ray_buffers(rtow_scene *s, uint64_t n) {
+    if (n <= s->ray_cap) return RTOW_OK;
+    if (s->d_rays) cudaFree(s->d_rays);
+    if (s->d_hits) cudaFree(s->d_hits);
+    s->d_rays = s->d_hits = nullptr; s->ray_cap = 0;
+    CUDA_TRY(cudaMalloc(&s->d_rays, n * sizeof(rtow_ray)));
+    CUDA_TRY(cudaMalloc(&s->d_hits, n * sizeof(rtow_hit)));
+    s->ray_cap = n;
+    return RTOW_OK;
+}
+
+int ensure_image_buffers(rtow_scene *s, size_t pixels) {
+    if (pixels <= s->img_cap) return RTOW_OK;
+    if (s->d_accum) cudaFree(s->d_accum);
+    if (s->d_rgb) cudaFree(s->d_rgb);
+    if (s->d_bgra) cudaFree(s->d_bgra);
+    s->d_accum = s->d_rgb = nullptr; s->d_bgra = nullptr; s->img_cap = 0;
+    CUDA_TRY(cudaMalloc((void **)&s->d_accum, pixels * 3 * sizeof(float)));
+    CUDA_TRY(cudaMalloc((void **)&s->d_rgb, pixels * 3 * sizeof(float)));
+    CUDA_TRY(cudaMalloc((void **)&s->d_bgra, pixels * 4));
+    s->img_cap = pixels;
+    return RTOW_OK;
+}
+
+int resolve_traverse(const rtow_scene *s, int traverse, int *out) {
+    if (traverse == RTOW_TRAVERSE_AUTO) traverse = s->has_fast ? RTOW_TRAVERSE_FAST : RTOW_TRAVERSE_EXACT;
+    if (traverse != RTOW_TRAVERSE_EXACT && traverse != RTOW_TRAVERSE_FAST) return set_error(RTOW_ERR_INVALID_ARG, "unknown traverse mode");
+    if (traverse == RTOW_TRAVERSE_FAST && !s->has_fast) traverse = RTOW_TRAVERSE_EXACT;   // list scenes have nothing to cull
+    *out = traverse;
+    return RTOW_OK;
+}
+
+int check_render_args(const rtow_scene *s, const rtow_camera *cam, const rtow_render_params *p, RenderLaunch *L) {
+    if (!s || !cam || !p) return set_error(RTOW_ERR_INVALID_ARG, "render: null argument");
+    if (p->width <= 0 || p->height <= 0 || (long long)p->width * p->height > (1ll << 30)) return set_error(RTOW_ERR_INVALID_ARG, "render: bad image size");
+    if (p->spp <= 0 || p->sample_begin < 0 || p->sample_count < 0) return set_error(RTOW_ERR_INVALID_ARG, "render: bad sample range");
+    int count = p->sample_count > 0 ? p->sample_count : p->spp - p->sample_begin;
+    if (count <= 0 || (long long)p->sample_begin + count > p->spp) return set_error(RTOW_ERR_INVALID_ARG, "render: sample range exceeds spp");
+    if (p->max_depth < 0) return set_error(RTOW_ERR_INVALID_ARG, "render: negative max_depth");
+    if (p->kernel != RTOW_KERNEL_AUTO && p->kernel != RTOW_KERNEL_MEGA && p->kernel != RTOW_KERNEL_WAVEFRONT)
+        return set_error(RTOW_ERR_INVALID_ARG, "render: unknown kernel");
+    if (p->kernel == RTOW_KERNEL_WAVEFRONT) return set_error(RTOW_ERR_UNSUPPORTED, "render: wavefront kernels are not built in this version");
+    int trav;
+    if (int rc = resolve_traverse(s, p->traverse, &trav)) return rc;
+    L->width = p->width; L->height = p->height;
+    L->sample_begin = p->sample_begin; L->sample_count = count;
+    L->max_depth = p->max_depth; L->global_illum_en = p->global_illum_en;
+    int S = 32;
+    while (S > count) S >>= 1;
+    L->lanes_per_pixel = S;
+    L->traverse = trav;
+    L->sky_gain = p->sky_gain; L->ambient_gain = p->ambient_gain;
+    L->seed = p->seed;
+    return RTOW_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rtow_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char *rtow_build_info(void) {
+    return "rtow_b200 abi " "1" " | nvcc " __DATE__ " | sm_100a | -fmad=false | kernels: trace, render_mega, resolve";
+}
+
+void rtow_scene_destroy(rtow_scene *s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    for (void *p : s->allocs) cudaFree(p);
+    for (void *p : {(void *)s->d_counters, s->d_rays, s->d_hits, (void *)s->d_accum, (void *)s->d_rgb, (void *)s->d_bgra})
+        if (p) cudaFree(p);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    delete s;
+}
+
+int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out) {
+    if (!desc || !out) return set_error(RTOW_ERR_INVALID_ARG, "rtow_scene_create: null argument");
+    *out = nullptr;
+    if (int rc = validate(desc)) return rc;
+    int ndev = rtow_device_count();
+    if (ndev == 0) return set_error(RTOW_ERR_NO_DEVICE, "no CUDA device visible (this library has no CPU path)");
+    if (device < 0 || device >= ndev) return set_error(RTOW_ERR_INVALID_ARG, "device index out of range");
+    CUDA_TRY(cudaSetDevice(device));
+
+    rtow_scene *s = new rtow_scene;
+    s->device = device;
+    std::memset(&s->d, 0, sizeof s->d);
+    struct Guard { rtow_scene *s; ~Guard() { if (s) rtow_scene_destroy(s); } } guard{s};
+    DScene &D = s->d;
+    D.top_kind = desc->top_kind;
+    D.root_xf_begin = desc->root_xform_begin; D.root_xf_count = desc->root_xform_count;
+    D.n_prims = desc->n_prims; D.n_objects = desc->n_objects;
+    D.n_prims_top = desc->n_objects ? desc->objects[desc->n_objects - 1].prim_begin + desc->objects[desc->n_objects - 1].prim_count : 0;
+    D.has_perlin = desc->perlin ? 1 : 0;
+
+    int rc;
+    static_assert(sizeof(rtow_prim) == 80 && sizeof(rtow_xform) == 16, "POD layout");
+    if ((rc = upload(s, (const int4 *)desc->prims, (size_t)desc->n_prims * 5, &D.prims))) return rc;
+    if ((rc = upload(s, (const float4 *)desc->xforms, (size_t)desc->n_xforms, &D.xforms))) return rc;
+
+    std::vector<int4> objs(desc->n_objects);
+    for (int i = 0; i < desc->n_objects; ++i) {
+        const rtow_object &o = desc->objects[i];
+        int flags = 0;
+        for (int p = o.prim_begin; p < o.prim_begin + o.prim_count; ++p)
+            if (desc->prims[p].type == RTOW_PRIM_MEDIUM) flags |= 1;
+        objs[i] = make_int4(o.prim_begin, o.prim_count, flags, o.prim_count == 1 ? o.prim_begin : -1);
+    }
+    if ((rc = upload(s, objs.data(), objs.size(), &D.objects))) return rc;
+
+    std::vector<int4> mats((size_t)desc->n_materials * 2);
+    for (int i = 0; i < desc->n_materials; ++i) {
+        const rtow_material &m = desc->materials[i];
+        int32_t f[4]; std::memcpy(f, m.f, 16);
+        bool textured = m.type == RTOW_MAT_LAMBERTIAN || m.type == RTOW_MAT_DIFFUSE_LIGHT || m.type == RTOW_MAT_ISOTROPIC;
+        mats[2 * i] = make_int4(m.type, m.tex_id, f[0], f[1]);
+        mats[2 * i + 1] = make_int4(f[2], f[3], textured && texture_needs_uv(desc, m.tex_id) ? 1 : 0, 0);
+    }
+    if ((rc = upload(s, mats.data(), mats.size(), &D.materials))) return rc;
+
+    std::vector<int4> texs((size_t)desc->n_textures * 2);
+    for (int i = 0; i < desc->n_textures; ++i) {
+        const rtow_texture &t = desc->textures[i];
+        int32_t f[3]; std::memcpy(f, t.f, 12);
+        texs[2 * i] = make_int4(t.type, t.a, t.b, f[0]);
+        texs[2 * i + 1] = make_int4(f[1], f[2], 0, 0);
+    }
+    if ((rc = upload(s, texs.data(), texs.size(), &D.textures))) return rc;
+
+    std::vector<DImage> imgs(desc->n_images);
+    for (int i = 0; i < desc->n_images; ++i) {
+        const rtow_image &im = desc->images[i];
+        const uint8_t *dp = nullptr;
+        if ((rc = upload(s, im.data, (size_t)im.nx * im.ny * 3, &dp))) return rc;
+        imgs[i].data = dp; imgs[i].nx = im.nx; imgs[i].ny = im.ny;
+    }
+    if ((rc = upload(s, imgs.data(), imgs.size(), &D.images))) return rc;
+
+    if (desc->perlin) {
+        std::vector<float4> vec(256);
+        std::vector<uint8_t> perm(768);
+        for (int i = 0; i < 256; ++i) {
+            vec[i] = make_float4(desc->perlin->rand_vec[i][0], desc->perlin->rand_vec[i][1], desc->perlin->rand_vec[i][2], 0.f);
+            const int32_t *src[3] = {desc->perlin->perm_x, desc->perlin->perm_y, desc->perlin->perm_z};
+            for (int k = 0; k < 3; ++k) {
+                if (src[k][i] < 0 || src[k][i] > 255) return set_error(RTOW_ERR_INVALID_ARG, "perlin permutation entry outside 0..255");
+                perm[256 * k + i] = (uint8_t)src[k][i];
+            }
+        }
+        if ((rc = upload(s, vec.data(), vec.size(), &D.perlin_vec))) return rc;
+        if ((rc = upload(s, perm.data(), perm.size(), &D.perlin_perm))) return rc;
+    }
+    {
+        float lut[256];
+        for (int i = 0; i < 256; ++i) lut[i] = (float)(i / 255.0);   // texture.h:74-76
+        if ((rc = upload(s, lut, (size_t)256, &D.byte_to_float))) return rc;
+    }
+
+    if (desc->top_kind == RTOW_TOP_BVH) {
+        std::vector<Entry> entries;
+        entries.reserve((size_t)desc->n_nodes + desc->n_objects);
+        build_entries(desc, objs, entries);
+        D.n_entries = (int32_t)entries.size();
+        if ((rc = upload(s, (const float4 *)entries.data(), entries.size() * 2, &D.entries))) return rc;
+
+        FastBvh fb;
+        std::string why;
+        if (build_fast_bvh(desc, fb, &why) && fb.max_depth * 3 + 4 <= 64) {   // 64 = RTOW_FAST_STACK (rt_fast.cuh)
+            D.fast_n_nodes = (int32_t)(fb.nodes.size() / FAST_NODE_F4);
+            D.fast_root = fb.root;
+            for (int k = 0; k < 3; ++k) D.scene_center[k] = fb.center[k];
+            D.scene_radius = fb.radius;
+            D.fast_time_lo = fb.time_lo; D.fast_time_hi = fb.time_hi;
+            if ((rc = upload(s, fb.nodes.data(), fb.nodes.size(), &D.fast_nodes))) return rc;
+            if ((rc = upload(s, fb.leaves.data(), fb.leaves.size(), &D.fast_leaves))) return rc;
+            s->has_fast = true;
+        }
+    }
+
+    CUDA_TRY(cudaMalloc((void **)&s->d_counters, 4 * sizeof(unsigned long long)));
+    CUDA_TRY(cudaMemset(s->d_counters, 0, 4 * sizeof(unsigned long long)));
+    CUDA_TRY(cudaEventCreate(&s->ev0));
+    CUDA_TRY(cudaEventCreate(&s->ev1));
+    CUDA_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    guard.s = nullptr;
+    *out = s;
+    return RTOW_OK;
+}
+
+int rtow_trace_rays_device(rtow_scene *s, const rtow_ray *d_rays, uint64_t n, rtow_hit *d_hits, int traverse, uint64_t seed, void *stream) {
+    if (!s || (n && (!d_rays || !d_hits))) return set_error(RTOW_ERR_INVALID_ARG, "rtow_trace_rays_device: null argument");
+    if (n > (1ull << 39)) return set_error(RTOW_ERR_INVALID_ARG, "rtow_trace_rays_device: too many rays for one call");
+    int trav;
+    if (int rc = resolve_traverse(s, traverse, &trav)) return rc;
+    CUDA_TRY(cudaSetDevice(s->device));
+    launch_trace(s->d, d_rays, n, d_hits, trav, seed, s->d_counters, false, (cudaStream_t)stream);
+    CUDA_TRY(cudaGetLastError());
+    return RTOW_OK;
+}
+
+int rtow_trace_rays(rtow_scene *s, const rtow_ray *rays, uint64_t n, rtow_hit *hits, int traverse, uint64_t seed, rtow_stats *stats) {
+    if (!s || (n && (!rays || !hits))) return set_error(RTOW_ERR_INVALID_ARG, "rtow_trace_rays: null argument");
+    if (stats) std::memset(stats, 0, sizeof *stats);
+    if (n == 0) return RTOW_OK;
+    int trav;
+    if (int rc = resolve_traverse(s, traverse, &trav)) return rc;
+    CUDA_TRY(cudaSetDevice(s->device));
+    if (int rc = ensure_ray_buffers(s, n)) return rc;
+    cudaEvent_t t0, t1;
+    CUDA_TRY(cudaEventCreate(&t0)); CUDA_TRY(cudaEventCreate(&t1));
+    cudaStream_t st = s->stream;
+    CUDA_TRY(cudaEventRecord(t0, st));
+    CUDA_TRY(cudaMemcpyAsync(s->d_rays, rays, n * sizeof(rtow_ray), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaEventRecord(s->ev0, st));
+    launch_trace(s->d, (const rtow_ray *)s->d_rays, n, (rtow_hit *)s->d_hits, trav, seed, s->d_counters, false, st);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaEventRecord(s->ev1, st));
+    CUDA_TRY(cudaMemcpyAsync(hits, s->d_hits, n * sizeof(rtow_hit), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaEventRecord(t1, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (stats) {
+        stats->rays = n; stats->paths = 0; stats->launches = 1;
+        cudaEventElapsedTime(&stats->kernel_ms, s->ev0, s->ev1);
+        cudaEventElapsedTime(&stats->total_ms, t0, t1);
+    }
+    cudaEventDestroy(t0); cudaEventDestroy(t1);
+    return RTOW_OK;
+}
+
+int rtow_trace_counters(rtow_scene *s, const rtow_ray *rays, uint64_t n, int traverse, double *node_visits_per_ray, double *prim_tests_per_ray) {
+    if (!s || (n && !rays)) return set_error(RTOW_ERR_INVALID_ARG, "rtow_trace_counters: null argument");
+    if (node_visits_per_ray) *node_visits_per_ray = 0;
+    if (prim_tests_per_ray) *prim_tests_per_ray = 0;
+    if (n == 0) return RTOW_OK;
+    int trav;
+    if (int rc = resolve_traverse(s, traverse, &trav)) return rc;
+    CUDA_TRY(cudaSetDevice(s->device));
+    if (int rc = ensure_ray_buffers(s, n)) return rc;
+    cudaStream_t st = s->stream;
+    CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 4 * sizeof(unsigned long long), st));
+    CUDA_TRY(cudaMemcpyAsync(s->d_rays, rays, n * sizeof(rtow_ray), cudaMemcpyHostToDevice, st));
+    launch_trace(s->d, (const rtow_ray *)s->d_rays, n, (rtow_hit *)s->d_hits, trav, 0, s->d_counters, true, st);
+    CUDA_TRY(cudaGetLastError());
+    unsigned long long c[4];
+    CUDA_TRY(cudaMemcpyAsync(c, s->d_counters, sizeof c, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (node_visits_per_ray) *node_visits_per_ray = (double)c[2] / (double)n;
+    if (prim_tests_per_ray) *prim_tests_per_ray = (double)c[3] / (double)n;
+    return RTOW_OK;
+}
+
+int rtow_render_accumulate_device(rtow_scene *s, const rtow_camera *cam, const rtow_render_params *params, float *d_accum, void *stream) {
+    RenderLaunch L;
+    if (int rc = check_render_args(s, cam, params, &L)) return rc;
+    if (!d_accum) return set_error(RTOW_ERR_INVALID_ARG, "rtow_render_accumulate_device: null accumulator");
+    CUDA_TRY(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 4 * sizeof(unsigned long long), st));
+    CUDA_TRY(cudaEventRecord(s->ev0, st));
+    launch_render_mega(s->d, *cam, L, d_accum, s->d_counters, st);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaEventRecord(s->ev1, st));
+    s->pending = true;
+    s->pending_launches = 1;
+    return RTOW_OK;
+}
+
+int rtow_stream_stats(rtow_scene *s, void *stream, rtow_stats *stats) {
+    if (!s || !stats) return set_error(RTOW_ERR_INVALID_ARG, "rtow_stream_stats: null argument");
+    std::memset(stats, 0, sizeof *stats);
+    CUDA_TRY(cudaSetDevice(s->device));
+    CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+    if (!s->pending) return RTOW_OK;
+    unsigned long long c[4];
+    CUDA_TRY(cudaMemcpy(c, s->d_counters, sizeof c, cudaMemcpyDeviceToHost));
+    stats->rays = c[0]; stats->paths = c[1];
+    CUDA_TRY(cudaEventElapsedTime(&stats->kernel_ms, s->ev0, s->ev1));
+    stats->total_ms = stats->kernel_ms;
+    stats->launches = s->pending_launches;
+    return RTOW_OK;
+}
+
+int rtow_resolve_device(rtow_scene *s, const float *d_accum, int32_t width, int32_t height, int32_t spp, float *d_rgb_linear, uint8_t *d_bgra8,
+                        void *stream) {
+    if (!s || !d_accum || width <= 0 || height <= 0 || spp <= 0) return set_error(RTOW_ERR_INVALID_ARG, "rtow_resolve_device: bad argument");
+    CUDA_TRY(cudaSetDevice(s->device));
+    launch_resolve(d_accum, width, height, spp, d_rgb_linear, d_bgra8, (cudaStream_t)stream);
+    CUDA_TRY(cudaGetLastError());
+    return RTOW_OK;
+}
+
+int rtow_render(rtow_scene *s, const rtow_camera *cam, const rtow_render_params *params, float *rgb_linear_out, uint8_t *bgra8_out, rtow_stats *stats) {
+    RenderLaunch L;
+    if (int rc = check_render_args(s, cam, params, &L)) return rc;
+    if (stats) std::memset(stats, 0, sizeof *stats);
+    CUDA_TRY(cudaSetDevice(s->device));
+    size_t pixels = (size_t)params->width * params->height;
+    if (int rc = ensure_image_buffers(s, pixels)) return rc;
+    cudaStream_t st = s->stream;
+    cudaEvent_t t0, t1;
+    CUDA_TRY(cudaEventCreate(&t0)); CUDA_TRY(cudaEventCreate(&t1));
+    CUDA_TRY(cudaEventRecord(t0, st));
+    CUDA_TRY(cudaMemsetAsync(s->d_accum, 0, pixels * 3 * sizeof(float), st));
+    if (int rc = rtow_render_accumulate_device(s, cam, params, s->d_accum, st)) return rc;
+    // the mean is over the samples this call rendered
+    launch_resolve(s->d_accum, params->width, params->height, L.sample_count, rgb_linear_out ? s->d_rgb : nullptr, bgra8_out ? s->d_bgra : nullptr, st);
+    CUDA_TRY(cudaGetLastError());
+    if (rgb_linear_out) CUDA_TRY(cudaMemcpyAsync(rgb_linear_out, s->d_rgb, pixels * 3 * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (bgra8_out) CUDA_TRY(cudaMemcpyAsync(bgra8_out, s->d_bgra, pixels * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaEventRecord(t1, st));
+    rtow_stats tmp;
+    if (int rc = rtow_stream_stats(s, st, &tmp)) return rc;
+    if (stats) {
+        *stats = tmp;
+        cudaEventElapsedTime(&stats->total_ms, t0, t1);
+        stats->launches = tmp.launches + 1;
+    }
+    cudaEventDestroy(t0); cudaEventDestroy(t1);
+    return RTOW_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,292 @@
+// fast_bvh.cpp -- binned-SAH binary build over the scene's leaf objects, collapsed to 4-wide.
+// Host-side set-up code (like the reference's BvhNode constructor, bvhNode.h:25-59); nothing here
+// runs per ray.  See fast_bvh.h for what the structure is allowed to decide (culling only).
+#include "fast_bvh.h"
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+
+namespace rtow {
+namespace {
+
+struct DBox {
+    double lo[3], hi[3];
+    DBox() { for (int a = 0; a < 3; ++a) { lo[a] = 1e300; hi[a] = -1e300; } }
+    void grow(const DBox &b) { for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], b.lo[a]); hi[a] = std::max(hi[a], b.hi[a]); } }
+    void grow(const double p[3]) { for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], p[a]); hi[a] = std::max(hi[a], p[a]); } }
+    bool valid() const { return lo[0] <= hi[0]; }
+    double area() const {
+        double dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+        return 2 * (dx * dy + dy * dz + dz * dx);
+    }
+};
+
+// Box of `inner` (given in the space below the chain) expressed in the space above the chain.
+// chain ops map the RAY outer->inner (hitable.h:53-62,125-154): Translate o' = o - offset,
+// RotateY o' = (c*x - s*z, y, s*x + c*z).  Points go back with the inverse maps, innermost first.
+DBox chain_box(const rtow_xform *xf, int n, DBox b) {
+    for (int i = n - 1; i >= 0; --i) {
+        if (xf[i].type == RTOW_XF_TRANSLATE) {
+            for (int a = 0; a < 3; ++a) { b.lo[a] += xf[i].f[a]; b.hi[a] += xf[i].f[a]; }
+        } else if (xf[i].type == RTOW_XF_ROTATE_Y) {
+            double s = xf[i].f[0], c = xf[i].f[1];
+            DBox o;
+            for (int k = 0; k < 8; ++k) {
+                double x = (k & 1) ? b.hi[0] : b.lo[0], y = (k & 2) ? b.hi[1] : b.lo[1], z = (k & 4) ? b.hi[2] : b.lo[2];
+                double p[3] = {c * x + s * z, y, -s * x + c * z};
+                o.grow(p);
+            }
+            b = o;
+        }
+    }
+    return b;
+}
+
+bool prim_box(const rtow_scene_desc *d, int pid, DBox &out, float *tlo, float *thi, int depth = 0) {
+    const rtow_prim &p = d->prims[pid];
+    DBox b;
+    switch (p.type) {
+    case RTOW_PRIM_SPHERE:
+        for (int a = 0; a < 3; ++a) { b.lo[a] = (double)p.f[a] - std::fabs((double)p.f[3]); b.hi[a] = (double)p.f[a] + std::fabs((double)p.f[3]); }
+        break;
+    case RTOW_PRIM_MOVING_SPHERE: {
+        double r = std::fabs((double)p.f[8]);
+        for (int a = 0; a < 3; ++a) {
+            b.lo[a] = std::min((double)p.f[a], (double)p.f[3 + a]) - r;
+            b.hi[a] = std::max((double)p.f[a], (double)p.f[3 + a]) + r;
+        }
+        // centre(time) stays inside this box only for time in [time0, time1] (sphere.h:129-131)
+        float a0 = std::min(p.f[6], p.f[7]), a1 = std::max(p.f[6], p.f[7]);
+        *tlo = std::max(*tlo, a0); *thi = std::min(*thi, a1);
+        break;
+    }
+    case RTOW_PRIM_RECT_XY: b.lo[0] = p.f[0]; b.hi[0] = p.f[1]; b.lo[1] = p.f[2]; b.hi[1] = p.f[3]; b.lo[2] = b.hi[2] = p.f[4]; break;
+    case RTOW_PRIM_RECT_XZ: b.lo[0] = p.f[0]; b.hi[0] = p.f[1]; b.lo[2] = p.f[2]; b.hi[2] = p.f[3]; b.lo[1] = b.hi[1] = p.f[4]; break;
+    case RTOW_PRIM_RECT_YZ: b.lo[1] = p.f[0]; b.hi[1] = p.f[1]; b.lo[2] = p.f[2]; b.hi[2] = p.f[3]; b.lo[0] = b.hi[0] = p.f[4]; break;
+    case RTOW_PRIM_MEDIUM: {
+        if (depth > 0) return false;
+        for (int c = p.child_begin; c < p.child_begin + p.child_count; ++c) {
+            DBox cb;
+            if (!prim_box(d, c, cb, tlo, thi, depth + 1)) return false;
+            b.grow(cb);
+        }
+        break;
+    }
+    default: return false;
+    }
+    for (int a = 0; a < 3; ++a) {
+        if (!(b.lo[a] <= b.hi[a]) || !std::isfinite(b.lo[a]) || !std::isfinite(b.hi[a])) return false;
+    }
+    out = chain_box(d->xforms + p.xform_begin, p.xform_count, b);
+    return true;
+}
+
+struct BNode {
+    DBox box;
+    int left = -1, right = -1;   // binary node indices
+    int obj = -1;                // >= 0: leaf
+};
+
+struct Builder {
+    const std::vector<DBox> &boxes;
+    std::vector<double> cx, cy, cz;
+    std::vector<int> idx;
+    std::vector<BNode> nodes;
+
+    explicit Builder(const std::vector<DBox> &b) : boxes(b) {
+        size_t n = b.size();
+        cx.resize(n); cy.resize(n); cz.resize(n); idx.resize(n);
+        for (size_t i = 0; i < n; ++i) {
+            cx[i] = 0.5 * (b[i].lo[0] + b[i].hi[0]); cy[i] = 0.5 * (b[i].lo[1] + b[i].hi[1]); cz[i] = 0.5 * (b[i].lo[2] + b[i].hi[2]);
+            idx[i] = (int)i;
+        }
+    }
+    double cen(int o, int a) const { return a == 0 ? cx[o] : a == 1 ? cy[o] : cz[o]; }
+
+    int build(int b, int e) {
+        int me = (int)nodes.size();
+        nodes.emplace_back();
+        DBox bb, cb;
+        for (int i = b; i < e; ++i) {
+            bb.grow(boxes[idx[i]]);
+            double c[3] = {cx[idx[i]], cy[idx[i]], cz[idx[i]]};
+            cb.grow(c);
+        }
+        nodes[me].box = bb;
+        if (e - b == 1) { nodes[me].obj = idx[b]; return me; }
+        const int NB = 16;
+        int best_axis = -1, best_bin = -1;
+        double best_cost = 1e300;
+        for (int a = 0; a < 3; ++a) {
+            double lo = cb.lo[a], ext = cb.hi[a] - cb.lo[a];
+            if (!(ext > 0)) continue;
+            DBox bin_box[NB]; int bin_n[NB];
+            for (int k = 0; k < NB; ++k) bin_n[k] = 0;
+            double scale = NB / ext;
+            for (int i = b; i < e; ++i) {
+                int k = (int)((cen(idx[i], a) - lo) * scale);
+                k = k < 0 ? 0 : k >= NB ? NB - 1 : k;
+                bin_n[k]++; bin_box[k].grow(boxes[idx[i]]);
+            }
+            double right_area[NB]; int right_n[NB];
+            DBox acc; int cnt = 0;
+            for (int k = NB - 1; k > 0; --k) {
+                if (bin_n[k]) acc.grow(bin_box[k]);
+                cnt += bin_n[k];
+                right_area[k] = cnt ? acc.area() : 0; right_n[k] = cnt;
+            }
+            DBox accl; int cl = 0;
+            for (int k = 0; k < NB - 1; ++k) {
+                if (bin_n[k]) accl.grow(bin_box[k]);
+                cl += bin_n[k];
+                if (cl == 0 || right_n[k + 1] == 0) continue;
+                double cost = accl.area() * cl + right_area[k + 1] * right_n[k + 1];
+                if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = k; }
+            }
+        }
+        int mid;
+        if (best_axis < 0) {
+            mid = (b + e) / 2;   // all centroids coincide
+        } else {
+            double lo = cb.lo[best_axis], scale = NB / (cb.hi[best_axis] - cb.lo[best_axis]);
+            int a = best_axis, kb = best_bin;
+            auto it = std::partition(idx.begin() + b, idx.begin() + e, [&](int o) {
+                int k = (int)((cen(o, a) - lo) * scale);
+                k = k < 0 ? 0 : k >= NB ? NB - 1 : k;
+                return k <= kb;
+            });
+            mid = (int)(it - idx.begin());
+            if (mid == b || mid == e) mid = (b + e) / 2;
+        }
+        int l = build(b, mid);
+        int r = build(mid, e);
+        nodes[me].left = l; nodes[me].right = r;
+        return me;
+    }
+};
+
+inline float i2f(int32_t v) { float f; std::memcpy(&f, &v, 4); return f; }
+
+// outward-rounded float bounds with a little slack for the float arithmetic of the hit code
+inline float down(double v, double pad) { float f = (float)(v - pad); while ((double)f > v - pad) f = std::nextafterf(f, -FLT_MAX); return f; }
+inline float up(double v, double pad) { float f = (float)(v + pad); while ((double)f < v + pad) f = std::nextafterf(f, FLT_MAX); return f; }
+
+}  // namespace
+
+bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
+    auto fail = [&](const char *m) { if (why) *why = m; return false; };
+    if (d->top_kind != RTOW_TOP_BVH || d->n_objects < 1) return fail("not a BVH scene");
+    const int n = d->n_objects;
+    float tlo = -FLT_MAX, thi = FLT_MAX;
+
+    std::vector<DBox> boxes(n);
+    DBox world;
+    for (int o = 0; o < n; ++o) {
+        const rtow_object &ob = d->objects[o];
+        if (ob.prim_count < 1) return fail("empty object");
+        for (int p = ob.prim_begin; p < ob.prim_begin + ob.prim_count; ++p) {
+            DBox pb;
+            if (!prim_box(d, p, pb, &tlo, &thi)) return fail("primitive without a finite box");
+            boxes[o].grow(pb);
+        }
+        world.grow(boxes[o]);
+    }
+    double ext = 0;
+    for (int a = 0; a < 3; ++a) ext = std::max(ext, std::max(std::fabs(world.lo[a]), std::fabs(world.hi[a])));
+    for (int a = 0; a < 3; ++a) out.center[a] = (float)(0.5 * (world.lo[a] + world.hi[a]));
+    double rad = 0;
+    for (int a = 0; a < 3; ++a) { double h = 0.5 * (world.hi[a] - world.lo[a]); rad += h * h; }
+    out.radius = (float)(std::sqrt(rad) * 1.0001 + 1e-6);
+    out.time_lo = tlo; out.time_hi = thi;
+
+    // guard boxes: the reference node that owns each leaf (bvhNode.h:12-23)
+    std::vector<int> owner(n, -1);
+    std::vector<char> twice(n, 0);
+    for (int i = 0; i < d->n_nodes; ++i) {
+        const rtow_bvh_node &nd = d->nodes[i];
+        if (nd.left < 0) { if (owner[~nd.left] >= 0) return fail("object referenced by two nodes"); owner[~nd.left] = i; }
+        if (nd.right < 0 && nd.right != nd.left) { if (owner[~nd.right] >= 0) return fail("object referenced by two nodes"); owner[~nd.right] = i; }
+        if (nd.left < 0 && nd.right == nd.left) twice[~nd.left] = 1;
+    }
+    out.leaves.assign((size_t)n * FAST_LEAF_F4, make_float4(0, 0, 0, 0));
+    for (int o = 0; o < n; ++o) {
+        if (owner[o] < 0) return fail("object not referenced by the tree");
+        const rtow_bvh_node &g = d->nodes[owner[o]];
+        const rtow_object &ob = d->objects[o];
+        const rtow_prim &p0 = d->prims[ob.prim_begin];
+        bool simple = ob.prim_count == 1 && p0.type == RTOW_PRIM_SPHERE && p0.xform_count == 0;
+        bool has_medium = false;
+        for (int p = ob.prim_begin; p < ob.prim_begin + ob.prim_count; ++p) has_medium |= d->prims[p].type == RTOW_PRIM_MEDIUM;
+        int kind = simple ? 1 : 0;   // ENTRY_SPHERE / ENTRY_OBJECT
+        if (twice[o] && has_medium) kind |= FAST_LEAF_TWICE;
+        out.leaves[(size_t)o * 3 + 0] = make_float4(g.bmin[0], g.bmin[1], g.bmin[2], i2f(o));
+        out.leaves[(size_t)o * 3 + 1] = make_float4(g.bmax[0], g.bmax[1], g.bmax[2], i2f(kind));
+        if (simple) out.leaves[(size_t)o * 3 + 2] = make_float4(p0.f[0], p0.f[1], p0.f[2], p0.f[3]);
+    }
+
+    Builder B(boxes);
+    B.nodes.reserve((size_t)2 * n);
+    int broot = B.build(0, n);
+
+    // collapse to 4-wide, depth first
+    const double pad_rel = 4e-7;
+    struct Item { int bnode; int slot_node; int slot; int depth; };
+    out.nodes.clear();
+    out.nodes.reserve((size_t)n / 2 * FAST_NODE_F4);
+    std::vector<Item> stack;
+    auto new_node = [&]() {
+        int id = (int)(out.nodes.size() / FAST_NODE_F4);
+        for (int k = 0; k < FAST_NODE_F4; ++k) out.nodes.push_back(make_float4(0, 0, 0, 0));
+        float4 &refs = out.nodes[(size_t)id * FAST_NODE_F4 + 6];
+        refs = make_float4(i2f(FAST_EMPTY), i2f(FAST_EMPTY), i2f(FAST_EMPTY), i2f(FAST_EMPTY));
+        return id;
+    };
+    auto set_lane = [](float4 &v, int k, float x) { (k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w) = x; };
+    out.root = new_node();
+    stack.push_back({broot, -1, -1, 1});
+    out.max_depth = 1;
+    bool first = true;
+    while (!stack.empty()) {
+        Item it = stack.back(); stack.pop_back();
+        out.max_depth = std::max(out.max_depth, it.depth);
+        int id;
+        if (first) { id = out.root; first = false; }
+        else {
+            id = new_node();
+            set_lane(out.nodes[(size_t)it.slot_node * FAST_NODE_F4 + 6], it.slot, i2f(id));
+        }
+        int kids[4]; int nk = 0;
+        const BNode &bn = B.nodes[it.bnode];
+        if (bn.obj >= 0) { kids[nk++] = it.bnode; }
+        else {
+            kids[nk++] = bn.left; kids[nk++] = bn.right;
+            while (nk < 4) {
+                int pick = -1; double pa = -1;
+                for (int k = 0; k < nk; ++k) {
+                    const BNode &c = B.nodes[kids[k]];
+                    if (c.obj < 0 && c.box.area() > pa) { pa = c.box.area(); pick = k; }
+                }
+                if (pick < 0) break;
+                int c = kids[pick];
+                kids[pick] = B.nodes[c].left;
+                kids[nk++] = B.nodes[c].right;
+            }
+        }
+        for (int k = 0; k < nk; ++k) {
+            const BNode &c = B.nodes[kids[k]];
+            float4 *nd = &out.nodes[(size_t)id * FAST_NODE_F4];
+            for (int a = 0; a < 3; ++a) {
+                double pad = pad_rel * (ext + std::fabs(c.box.lo[a]) + std::fabs(c.box.hi[a])) + 1e-30;
+                set_lane(nd[2 * a], k, down(c.box.lo[a], pad));
+                set_lane(nd[2 * a + 1], k, up(c.box.hi[a], pad));
+            }
+            if (c.obj >= 0) set_lane(nd[6], k, i2f(~c.obj));
+            else stack.push_back({kids[k], id, k, it.depth + 1});
+        }
+    }
+    return true;
+}
+
+}  // namespace rtow

@@ -1,0 +1,45 @@
+// fast_bvh.h -- host-side builder of the library's own traversal structure (RTOW_TRAVERSE_FAST).
+//
+// The reference's BvhNode tree (random split axis, object median, no distance culling:
+// bvhNode.h:25-96) is kept for RTOW_TRAVERSE_EXACT.  For speed the library builds a 4-wide SAH
+// BVH over the same leaf objects.  It is used ONLY to cull: a leaf found through it is accepted
+// iff the reference would accept it, which is decided by the leaf's *guard box* -- the box of the
+// reference node that owns the leaf -- tested with the reference's own slab arithmetic
+// (aabb.h:22-43).  Slab tests are monotone under box inclusion and every ancestor box contains
+// the parent's, so "parent box passes" == "all ancestor boxes pass" == the reference reaches the
+// leaf.  See DESIGN.md for the argument and for the culling slack.
+#pragma once
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>   // float4
+
+#include "../../include/rtow_b200.h"
+
+namespace rtow {
+
+// Node = 8 x float4 (128 B, one cache line):
+//   [0] lo.x of the 4 children  [1] hi.x  [2] lo.y  [3] hi.y  [4] lo.z  [5] hi.z
+//   [6] child refs as int bits: >= 0 node index, < 0 leaf = ~ref, FAST_EMPTY = no child
+//   [7] unused
+enum { FAST_NODE_F4 = 8, FAST_LEAF_F4 = 3 };
+static const int32_t FAST_EMPTY = 0x7fffffff;
+enum { FAST_LEAF_TWICE = 0x100 };   // ORed into the leaf kind: n==1 node, evaluate a medium twice
+
+struct FastBvh {
+    std::vector<float4> nodes;    // FAST_NODE_F4 per node
+    std::vector<float4> leaves;   // FAST_LEAF_F4 per object, indexed by object id
+    int32_t root = 0;
+    float center[3] = {0, 0, 0};
+    float radius = 0;             // bounds every primitive box and centre, from `center`
+    float time_lo = 0, time_hi = 0;   // ray times for which moving-sphere boxes are valid
+    int max_depth = 0;
+};
+
+// Returns false (with a reason) when the scene cannot use the fast structure; the caller then
+// serves FAST requests with the exact walk.
+bool build_fast_bvh(const rtow_scene_desc *desc, FastBvh &out, std::string *why);
+
+}  // namespace rtow

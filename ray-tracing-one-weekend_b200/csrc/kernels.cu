@@ -1,0 +1,231 @@
+// kernels.cu -- the sm_100a kernels of the hot path:
+//   trace_kernel        world->hit() on a batch of rays                    (hitable.h:21)
+//   render_mega_kernel  pixel/sample loop + color() as one persistent-lane megakernel
+//                       (main.cpp:932-956, color.h:12-59, camera.h:123-135)
+//   resolve_kernel      mean, sqrt tone curve, 255.99 quantisation, BGRA8  (main.cpp:955-989)
+// Built with -fmad=false: see rt_device.cuh.
+#include "rt_kernels.cuh"
+#include "rt_shade.cuh"
+#include "rt_fast.cuh"
+
+namespace rtow {
+
+template <bool COUNT>
+__device__ __forceinline__ bool closest_hit(const DScene &S, int traverse, const Ray &r, float tmin, float tmax, const Rng *g, float &t, int &pid,
+                                            unsigned &nv, unsigned &pt) {
+    if (traverse == RTOW_TRAVERSE_FAST) return closest_hit_fast<COUNT>(S, r, tmin, tmax, g, t, pid, nv, pt);
+    return closest_hit_exact<COUNT>(S, r, tmin, tmax, g, t, pid, nv, pt);
+}
+
+// ---- trace ------------------------------------------------------------------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(256) trace_kernel(DScene S, const rtow_ray *__restrict__ rays, uint64_t n, rtow_hit *__restrict__ hits,
+                                                    int traverse, uint64_t seed, unsigned long long *__restrict__ counters) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned nv = 0, pt = 0;
+    if (i < n) {
+        const float *q = reinterpret_cast<const float *>(rays + i);
+        Ray r;
+        r.ox = __ldg(q + 0); r.oy = __ldg(q + 1); r.oz = __ldg(q + 2);
+        r.dx = __ldg(q + 3); r.dy = __ldg(q + 4); r.dz = __ldg(q + 5);
+        r.time = __ldg(q + 6);
+        float tmin = __ldg(q + 7), tmax = __ldg(q + 8);
+        Rng g;
+        rng_init(g, seed, (uint32_t)i, (uint32_t)(i >> 32));
+        chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, r);
+        float t; int pid;
+        float4 o0, o1, o2;
+        if (closest_hit<COUNT>(S, traverse, r, tmin, tmax, &g, t, pid, nv, pt)) {
+            Hit h;
+            prim_record(S, pid, r, t, true, h);
+            o0 = make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.mat), h.n[0]);
+            o1 = make_float4(h.n[1], h.n[2], h.p[0], h.p[1]);
+            o2 = make_float4(h.p[2], h.u, h.v, 0.f);
+        } else {
+            o0 = make_float4(0.f, __int_as_float(-1), __int_as_float(-1), 0.f);
+            o1 = make_float4(0.f, 0.f, 0.f, 0.f);
+            o2 = o1;
+        }
+        float4 *out = reinterpret_cast<float4 *>(hits + i);
+        out[0] = o0; out[1] = o1; out[2] = o2;
+    }
+    if (COUNT) {
+        // warp-aggregate then one atomic per warp
+        for (int off = 16; off; off >>= 1) {
+            nv += __shfl_down_sync(0xffffffffu, nv, off);
+            pt += __shfl_down_sync(0xffffffffu, pt, off);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(&counters[2], (unsigned long long)nv);
+            atomicAdd(&counters[3], (unsigned long long)pt);
+        }
+    }
+}
+
+void launch_trace(const DScene &S, const rtow_ray *d_rays, uint64_t n, rtow_hit *d_hits, int traverse, uint64_t seed,
+                  unsigned long long *d_counters, bool count, cudaStream_t stream) {
+    if (n == 0) return;
+    unsigned blocks = (unsigned)((n + 255) / 256);
+    if (count) trace_kernel<true><<<blocks, 256, 0, stream>>>(S, d_rays, n, d_hits, traverse, seed, d_counters);
+    else trace_kernel<false><<<blocks, 256, 0, stream>>>(S, d_rays, n, d_hits, traverse, seed, d_counters);
+}
+
+// ---- render: megakernel -----------------------------------------------------------------
+// A warp owns 32/S pixels; lane (p, j) runs samples j, j+S, ... of its pixel.  Every lane is a
+// persistent path tracer: when its path ends it starts its next sample at once (the bounce loop
+// is flat), so lanes of a warp stay busy until their own sample list is exhausted.  Partial sums
+// are combined with shuffles in a fixed order -> the image is deterministic for a seed.
+__global__ void __launch_bounds__(256) render_mega_kernel(DScene S, rtow_camera cam, RenderLaunch L, float *__restrict__ accum,
+                                                          unsigned long long *__restrict__ counters) {
+    __shared__ PerlinSmem perlin;
+    perlin_stage(S, &perlin);
+    __syncthreads();
+
+    const int Sl = L.lanes_per_pixel;
+    const int ppw = 32 / Sl;                                  // pixels per warp
+    const int lane = threadIdx.x & 31;
+    const unsigned warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int n_pixels = L.width * L.height;
+    const long long pixel_ll = (long long)warp_global * ppw + lane / Sl;
+    const bool pixel_ok = pixel_ll < n_pixels;
+    const int pixel = pixel_ok ? (int)pixel_ll : 0;
+    const int lane_s = lane % Sl;
+    const int x = pixel % L.width, y = pixel / L.width;
+    const int row = L.height - 1 - y;                         // the reference counts rows from the bottom (main.cpp:932)
+
+    float acc[3] = {0.f, 0.f, 0.f};
+    unsigned long long rays = 0, paths = 0;
+    unsigned nv = 0, pt = 0;
+
+    int s = lane_s - Sl;                                      // next sample index (relative) = s + Sl
+    bool alive = false;
+    Ray r;
+    Rng g;
+    float T[3], Lr[3];
+    int depth = 0;
+    r.ox = r.oy = r.oz = r.dx = r.dy = r.dz = r.time = 0.f;
+    T[0] = T[1] = T[2] = 1.f; Lr[0] = Lr[1] = Lr[2] = 0.f;
+    rng_init(g, L.seed, 0, 0);
+
+    for (;;) {
+        if (!alive) {
+            s += Sl;
+            if (!pixel_ok || s >= L.sample_count) break;
+            rng_init(g, L.seed, (uint32_t)pixel, (uint32_t)(L.sample_begin + s));
+            float ju = rng_next(g), jv = rng_next(g);
+            float u = (float)((double)x + (double)ju) / (float)L.width;       // main.cpp:943-944
+            float v = (float)((double)row + (double)jv) / (float)L.height;
+            camera_ray(cam, u, v, g, r);
+            T[0] = T[1] = T[2] = 1.f; Lr[0] = Lr[1] = Lr[2] = 0.f;
+            depth = 0; alive = true; paths++;
+        }
+        // ---- color.h:12-59, iterative: L += T*E ; T *= A ----
+        g.bounce = (uint32_t)depth;
+        rays++;
+        Ray rl = r;
+        chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, rl);
+        float t; int pid;
+        if (!closest_hit<false>(S, L.traverse, rl, 0.001f, FLT_MAX, &g, t, pid, nv, pt)) {
+            if (L.global_illum_en) {
+                if (depth < 1) {                                              // color.h:35-50
+                    float ux, uy, uz;
+                    unit3(r.dx, r.dy, r.dz, ux, uy, uz);
+                    float k = (float)(1.0 + (double)uz);
+                    float sky0 = (float)((double)k * 0.1), sky1 = (float)((double)k * 0.3), sky2 = (float)((double)k * 1.0);
+                    Lr[0] += T[0] * (L.sky_gain * sky0); Lr[1] += T[1] * (L.sky_gain * sky1); Lr[2] += T[2] * (L.sky_gain * sky2);
+                } else {                                                      // color.h:52-54
+                    Lr[0] += T[0] * L.ambient_gain; Lr[1] += T[1] * L.ambient_gain; Lr[2] += T[2] * L.ambient_gain;
+                }
+            }
+            alive = false;
+        } else {
+            MatRec m = load_material(S, __ldg(&S.prims[pid * 5]).y);
+            Hit h;
+            prim_record(S, pid, rl, t, m.needs_uv != 0, h);
+            float em[3];
+            if (depth < L.max_depth) {
+                float atten[3], sd[3], st;
+                float rd[3] = {r.dx, r.dy, r.dz};
+                bool go = scatter(S, &perlin, m, h, rd, r.time, g, atten, sd, st, em);
+                Lr[0] += T[0] * em[0]; Lr[1] += T[1] * em[1]; Lr[2] += T[2] * em[2];
+                if (go) {
+                    T[0] *= atten[0]; T[1] *= atten[1]; T[2] *= atten[2];
+                    r.ox = h.p[0]; r.oy = h.p[1]; r.oz = h.p[2];
+                    r.dx = sd[0]; r.dy = sd[1]; r.dz = sd[2];
+                    r.time = st;
+                    depth++;
+                } else {
+                    alive = false;
+                }
+            } else {
+                // color.h:25-30: past the depth limit only `emitted` survives
+                if (m.type == RTOW_MAT_DIFFUSE_LIGHT) {
+                    texture_value(S, &perlin, m.tex, h.u, h.v, h.p, em);
+                    Lr[0] += T[0] * em[0]; Lr[1] += T[1] * em[1]; Lr[2] += T[2] * em[2];
+                }
+                alive = false;
+            }
+        }
+        if (!alive) { acc[0] += Lr[0]; acc[1] += Lr[1]; acc[2] += Lr[2]; }
+    }
+
+    // fixed-order reduction over the S lanes of a pixel
+    for (int off = Sl >> 1; off; off >>= 1) {
+        acc[0] += __shfl_down_sync(0xffffffffu, acc[0], off);
+        acc[1] += __shfl_down_sync(0xffffffffu, acc[1], off);
+        acc[2] += __shfl_down_sync(0xffffffffu, acc[2], off);
+    }
+    if (pixel_ok && lane_s == 0) {
+        float *px = accum + (size_t)pixel * 3;
+        px[0] += acc[0]; px[1] += acc[1]; px[2] += acc[2];
+    }
+    for (int off = 16; off; off >>= 1) {
+        rays += __shfl_down_sync(0xffffffffu, rays, off);
+        paths += __shfl_down_sync(0xffffffffu, paths, off);
+    }
+    if (lane == 0) {
+        atomicAdd(&counters[0], rays);
+        atomicAdd(&counters[1], paths);
+    }
+}
+
+void launch_render_mega(const DScene &S, const rtow_camera &cam, const RenderLaunch &L, float *d_accum,
+                        unsigned long long *d_counters, cudaStream_t stream) {
+    long long n_pixels = (long long)L.width * L.height;
+    int ppw = 32 / L.lanes_per_pixel;
+    long long warps = (n_pixels + ppw - 1) / ppw;
+    long long blocks = (warps + 7) / 8;
+    render_mega_kernel<<<(unsigned)blocks, 256, 0, stream>>>(S, cam, L, d_accum, d_counters);
+}
+
+// ---- resolve: main.cpp:955-989 -------------------------------------------------------------
+__global__ void resolve_kernel(const float *__restrict__ accum, int n_pixels, float inv_spp, float *__restrict__ rgb, uint8_t *__restrict__ bgra) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pixels) return;
+    float c[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) c[k] = accum[(size_t)p * 3 + k] * inv_spp;   // vec3.h:133-139: multiply by float(1.0/spp)
+    if (rgb) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) rgb[(size_t)p * 3 + k] = c[k];
+    }
+    if (bgra) {
+        unsigned q[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            float sq = sqrtf(c[k]);                        // main.cpp:956
+            double sc = 255.99 * (double)sq;               // main.cpp:963-965, product in double
+            unsigned v = sc > 0.0 ? (unsigned)(unsigned short)(int)fmin(sc, 65535.0) : 0u;
+            q[k] = v > 255u ? 255u : v;                    // main.cpp:968-970
+        }
+        reinterpret_cast<uchar4 *>(bgra)[p] = make_uchar4((unsigned char)q[2], (unsigned char)q[1], (unsigned char)q[0], 0);
+    }
+}
+
+void launch_resolve(const float *d_accum, int width, int height, int spp, float *d_rgb, uint8_t *d_bgra, cudaStream_t stream) {
+    int n = width * height;
+    float inv = (float)(1.0 / (double)(float)spp);
+    resolve_kernel<<<(n + 255) / 256, 256, 0, stream>>>(d_accum, n, inv, d_rgb, d_bgra);
+}
+
+}  // namespace rtow

@@ -1,0 +1,375 @@
+// rt_device.cuh -- device-side scene layout and the ray/primitive arithmetic of the hot path.
+//
+// Every float expression on the hit path keeps the reference's operation order and is
+// compiled without FMA contraction (the TU is built with -fmad=false; IEEE '/' and sqrtf are
+// nvcc's defaults), because the parity gate is bit-exact primitive/material ids and t against
+// the reference's CPU code.  Citations are relative to /root/reference/rayTracingOneWeekend/.
+#pragma once
+
+#include <cfloat>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/rtow_b200.h"
+
+namespace rtow {
+
+// ---- device scene ----------------------------------------------------------------------
+struct DImage {
+    const uint8_t *data;   // RGB8, row 0 first
+    int nx, ny;
+};
+
+// Threaded (stackless) pre-order form of the reference's BvhNode tree.  Entry i = 2 x float4.
+//   internal: a = {bmin.xyz, escape index}, b = {bmax.xyz, -1}
+//   leaf:     a = {cx,cy,cz,r} (kind SPHERE) or unused, b = {prim/obj id, visit, 0, kind}
+// Pre-order = the reference's left-then-right recursion, so leaves come up in in-order and the
+// tie rule `left.t < right.t ? left : right` (bvhNode.h:74-77) is "t <= best replaces".
+enum { ENTRY_NODE = -1, ENTRY_OBJECT = 0, ENTRY_SPHERE = 1 };
+
+struct DScene {
+    int32_t top_kind;
+    int32_t root_xf_begin, root_xf_count;
+    int32_t n_entries;
+    int32_t n_prims_top;          // LIST mode: the root run is prims[0, n_prims_top)
+    int32_t n_prims, n_objects;
+    int32_t has_perlin;
+    const float4 *entries;
+    const int4 *objects;          // {prim_begin, prim_count, flags(bit0: contains a medium), single-prim id or -1}
+    const int4 *prims;            // rtow_prim as 5 x int4
+    const float4 *xforms;         // rtow_xform as float4 {type bits, f0, f1, f2}
+    const int4 *materials;        // rtow_material as {type, tex, f0, f1}, {f2, f3, -, -}  (stored 2 x int4)
+    const int4 *textures;         // rtow_texture as {type, a, b, f0}, {f1, f2, -, -}
+    const DImage *images;
+    const float4 *perlin_vec;     // 256 gradients
+    const uint8_t *perlin_perm;   // x[256] y[256] z[256]
+    const float *byte_to_float;   // 256 entries (float)(i / 255.0)  texture.h:74-76
+    // fast structure (may be null)
+    int32_t fast_n_nodes, fast_root;
+    const float4 *fast_nodes;     // 8 x float4 per node (fast_bvh.h)
+    const float4 *fast_leaves;    // 3 x float4 per object: guard box, ids, sphere (fast_bvh.h)
+    float scene_center[3];
+    float scene_radius;           // bounds all primitive boxes (for the culling slack)
+    float fast_time_lo, fast_time_hi;   // ray times for which the moving-sphere cull boxes hold
+};
+
+struct Ray {
+    float ox, oy, oz, dx, dy, dz, time;
+};
+
+// ---- Philox4x32-10: the sample-stream spec shared with oracle/rtow_oracle.c ------------------
+struct Rng {
+    uint32_t k0, k1, pixel, sample, next, blk, bounce;
+    uint32_t b0, b1, b2, b3;
+};
+
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1,
+                                              uint32_t &o0, uint32_t &o1, uint32_t &o2, uint32_t &o3) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    o0 = c0; o1 = c1; o2 = c2; o3 = c3;
+}
+
+__device__ __forceinline__ float u01_from_bits(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
+
+__device__ __forceinline__ void rng_init(Rng &g, uint64_t seed, uint32_t pixel, uint32_t sample) {
+    g.k0 = (uint32_t)seed; g.k1 = (uint32_t)(seed >> 32);
+    g.pixel = pixel; g.sample = sample; g.next = 0; g.blk = 0xffffffffu; g.bounce = 0;
+}
+// draw k of the path stream = lane k%4 of block k/4, counter (pixel, sample, block, 0)
+__device__ __forceinline__ float rng_next(Rng &g) {
+    uint32_t blk = g.next >> 2, lane = g.next & 3u;
+    if (blk != g.blk) {
+        philox4x32_10(g.pixel, g.sample, blk, 0u, g.k0, g.k1, g.b0, g.b1, g.b2, g.b3);
+        g.blk = blk;
+    }
+    g.next++;
+    uint32_t x = lane == 0 ? g.b0 : lane == 1 ? g.b1 : lane == 2 ? g.b2 : g.b3;
+    return u01_from_bits(x);
+}
+// medium free-flight draws have their own counter space so they do not depend on traversal order
+__device__ __forceinline__ float rng_medium(const Rng &g, int prim_id, int visit) {
+    uint32_t o0, o1, o2, o3;
+    philox4x32_10(g.pixel, g.sample, g.bounce * 2u + (uint32_t)visit, 1u + (uint32_t)prim_id, g.k0, g.k1, o0, o1, o2, o3);
+    return u01_from_bits(o0);
+}
+
+// ---- vec helpers in the reference's evaluation order (vec3.h) --------------------------------
+__device__ __forceinline__ float dot3(float ax, float ay, float az, float bx, float by, float bz) {
+    return ax * bx + ay * by + az * bz;   // vec3.h:86-88, left to right, no contraction
+}
+__device__ __forceinline__ float len3(float x, float y, float z) { return sqrtf(x * x + y * y + z * z); }   // vec3.h:30-32
+__device__ __forceinline__ void unit3(float x, float y, float z, float &ox, float &oy, float &oz) {          // vec3.h:141-148
+    float l = len3(x, y, z);
+    if (l == 0.0f) { ox = oy = oz = 0.f; return; }
+    ox = x / l; oy = y / l; oz = z / l;
+}
+
+// ---- wrappers: Translate hitable.h:53-62, RotateY 125-154, FlipNormals 28-36 -----------------
+__device__ __forceinline__ void chain_ray(const float4 *__restrict__ xf, int begin, int n, Ray &r) {
+    for (int i = 0; i < n; ++i) {
+        float4 x = __ldg(&xf[begin + i]);
+        int type = __float_as_int(x.x);
+        if (type == RTOW_XF_TRANSLATE) {
+            r.ox = r.ox - x.y; r.oy = r.oy - x.z; r.oz = r.oz - x.w;
+        } else if (type == RTOW_XF_ROTATE_Y) {
+            float s = x.y, c = x.z;
+            float ox = c * r.ox - s * r.oz, oz = s * r.ox + c * r.oz;
+            float dx = c * r.dx - s * r.dz, dz = s * r.dx + c * r.dz;
+            r.ox = ox; r.oz = oz; r.dx = dx; r.dz = dz;
+        }
+    }
+}
+__device__ __forceinline__ void chain_hit(const float4 *__restrict__ xf, int begin, int n, float p[3], float nrm[3]) {
+    for (int i = n - 1; i >= 0; --i) {
+        float4 x = __ldg(&xf[begin + i]);
+        int type = __float_as_int(x.x);
+        if (type == RTOW_XF_TRANSLATE) {
+            p[0] += x.y; p[1] += x.z; p[2] += x.w;
+        } else if (type == RTOW_XF_ROTATE_Y) {
+            float s = x.y, c = x.z;
+            float px = c * p[0] + s * p[2], pz = -s * p[0] + c * p[2];
+            float nx = c * nrm[0] + s * nrm[2], nz = -s * nrm[0] + c * nrm[2];
+            p[0] = px; p[2] = pz; nrm[0] = nx; nrm[2] = nz;
+        } else {
+            nrm[0] = -nrm[0]; nrm[1] = -nrm[1]; nrm[2] = -nrm[2];
+        }
+    }
+}
+
+// ---- aabb.h:22-43: slab test in DIVISION form; ffmin/ffmax are a<b?a:b / a>b?a:b ---------------
+__device__ __forceinline__ bool aabb_hit(float bminx, float bminy, float bminz, float bmaxx, float bmaxy, float bmaxz,
+                                         const Ray &r, float tmin, float tmax) {
+    {
+        float ta = (bminx - r.ox) / r.dx, tb = (bmaxx - r.ox) / r.dx;
+        float t0 = ta < tb ? ta : tb, t1 = ta > tb ? ta : tb;
+        tmin = t0 > tmin ? t0 : tmin; tmax = t1 < tmax ? t1 : tmax;
+        if (tmax <= tmin) return false;
+    }
+    {
+        float ta = (bminy - r.oy) / r.dy, tb = (bmaxy - r.oy) / r.dy;
+        float t0 = ta < tb ? ta : tb, t1 = ta > tb ? ta : tb;
+        tmin = t0 > tmin ? t0 : tmin; tmax = t1 < tmax ? t1 : tmax;
+        if (tmax <= tmin) return false;
+    }
+    {
+        float ta = (bminz - r.oz) / r.dz, tb = (bmaxz - r.oz) / r.dz;
+        float t0 = ta < tb ? ta : tb, t1 = ta > tb ? ta : tb;
+        tmin = t0 > tmin ? t0 : tmin; tmax = t1 < tmax ? t1 : tmax;
+        if (tmax <= tmin) return false;
+    }
+    return true;
+}
+
+// ---- sphere.h:20-69 / 93-118: half-b quadratic, near root first then the far one ----------------
+__device__ __forceinline__ bool sphere_t(float cx, float cy, float cz, float radius, const Ray &r, float tmin, float tmax, float &t_out) {
+    float ocx = r.ox - cx, ocy = r.oy - cy, ocz = r.oz - cz;
+    float a = dot3(r.dx, r.dy, r.dz, r.dx, r.dy, r.dz);
+    float b = dot3(r.dx, r.dy, r.dz, ocx, ocy, ocz);
+    float cc = dot3(ocx, ocy, ocz, ocx, ocy, ocz) - radius * radius;
+    float disc = b * b - a * cc;
+    if (disc > 0) {
+        float sq = sqrtf(disc);
+        float temp = (-b - sq) / a;
+        if (temp < tmax && temp > tmin) { t_out = temp; return true; }
+        temp = (-b + sq) / a;
+        if (temp < tmax && temp > tmin) { t_out = temp; return true; }
+    }
+    return false;
+}
+
+// sphere.h:129-131
+__device__ __forceinline__ void moving_center(float c0x, float c0y, float c0z, float c1x, float c1y, float c1z, float t0, float t1,
+                                              float time, float &cx, float &cy, float &cz) {
+    float k = (time - t0) / (t1 - t0);
+    cx = c0x + k * (c1x - c0x); cy = c0y + k * (c1y - c0y); cz = c0z + k * (c1z - c0z);
+}
+
+// xy_rect.h:22-40, 57-75, 92-110: bounds inclusive, NaN-transparent like the reference
+__device__ __forceinline__ bool rect_t(float lo0, float hi0, float lo1, float hi1, float k, float o_ax, float d_ax, float o0, float d0,
+                                       float o1, float d1, float tmin, float tmax, float &t_out) {
+    float t = (k - o_ax) / d_ax;
+    if (t < tmin || t > tmax) return false;
+    float x = o0 + t * d0;
+    float y = o1 + t * d1;
+    if (x < lo0 || x > hi0 || y < lo1 || y > hi1) return false;
+    t_out = t;
+    return true;
+}
+
+struct PrimHead {
+    int type, mat_id, xf_begin, xf_count;
+};
+
+__device__ __forceinline__ PrimHead load_head(const int4 *__restrict__ prims, int pid) {
+    int4 h = __ldg(&prims[pid * 5]);
+    PrimHead p; p.type = h.x; p.mat_id = h.y; p.xf_begin = h.z; p.xf_count = h.w;
+    return p;
+}
+
+// One non-medium primitive behind its wrapper chain; r_in is in the enclosing aggregate's space.
+__device__ __forceinline__ bool simple_prim_t(const DScene &S, int pid, const PrimHead &p, const Ray &r_in, float tmin, float tmax, float &t_out) {
+    Ray r = r_in;
+    chain_ray(S.xforms, p.xf_begin, p.xf_count, r);
+    const float4 *f = reinterpret_cast<const float4 *>(S.prims + pid * 5 + 1);
+    float4 f0 = __ldg(&f[0]);
+    if (p.type == RTOW_PRIM_SPHERE) return sphere_t(f0.x, f0.y, f0.z, f0.w, r, tmin, tmax, t_out);
+    float4 f1 = __ldg(&f[1]);
+    if (p.type == RTOW_PRIM_MOVING_SPHERE) {
+        float4 f2 = __ldg(&f[2]);
+        float cx, cy, cz;
+        moving_center(f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w, r.time, cx, cy, cz);
+        return sphere_t(cx, cy, cz, f2.x, r, tmin, tmax, t_out);
+    }
+    if (p.type == RTOW_PRIM_RECT_XY) return rect_t(f0.x, f0.y, f0.z, f0.w, f1.x, r.oz, r.dz, r.ox, r.dx, r.oy, r.dy, tmin, tmax, t_out);
+    if (p.type == RTOW_PRIM_RECT_XZ) return rect_t(f0.x, f0.y, f0.z, f0.w, f1.x, r.oy, r.dy, r.ox, r.dx, r.oz, r.dz, tmin, tmax, t_out);
+    if (p.type == RTOW_PRIM_RECT_YZ) return rect_t(f0.x, f0.y, f0.z, f0.w, f1.x, r.ox, r.dx, r.oy, r.dy, r.oz, r.dz, tmin, tmax, t_out);
+    return false;
+}
+
+// hitableList.h:20-38 over a run of non-medium primitives (a medium's boundary)
+__device__ __forceinline__ bool run_hit_simple(const DScene &S, int begin, int count, const Ray &r, float tmin, float tmax, float &t_out) {
+    bool any = false;
+    float closest = tmax;
+    for (int i = begin; i < begin + count; ++i) {
+        PrimHead p = load_head(S.prims, i);
+        float t;
+        if (simple_prim_t(S, i, p, r, tmin, closest, t)) { any = true; closest = t; t_out = t; }
+    }
+    return any;
+}
+
+// constantMedium.h:26-74 (the discarded debug draw of line 27 is not reproduced)
+__device__ __forceinline__ bool medium_t(const DScene &S, int pid, const PrimHead &p, const Ray &r_in, float tmin, float tmax, const Rng *g,
+                                         int visit, float &t_out) {
+    Ray r = r_in;
+    chain_ray(S.xforms, p.xf_begin, p.xf_count, r);
+    float density = __int_as_float(__ldg(&S.prims[pid * 5 + 1]).x);
+    int4 tail = __ldg(&S.prims[pid * 5 + 4]);
+    int cb = tail.x, cn = tail.y;
+    float t1, t2;
+    if (!run_hit_simple(S, cb, cn, r, -FLT_MAX, FLT_MAX, t1)) return false;
+    if (!run_hit_simple(S, cb, cn, r, (float)((double)t1 + 0.0001), FLT_MAX, t2)) return false;
+    if (t1 < tmin) t1 = tmin;
+    if (t2 > tmax) t2 = tmax;
+    if (t1 >= t2) return false;
+    if (t1 < 0) t1 = 0;
+    float dlen = len3(r.dx, r.dy, r.dz);
+    float inside = (t2 - t1) * dlen;
+    float U = g ? rng_medium(*g, pid, visit) : 0.5f;
+    float hitDistance = (float)(-(double)(1 / density) * log((double)U));
+    if (hitDistance < inside) { t_out = t1 + hitDistance / dlen; return true; }
+    return false;
+}
+
+// hitableList.h:20-38 over a run of primitives: element i sees tmax = closest so far
+template <bool COUNT>
+__device__ __forceinline__ bool run_hit(const DScene &S, int begin, int count, const Ray &r, float tmin, float tmax, const Rng *g, int visit,
+                                        float &t_out, int &prim_out, unsigned &prim_tests) {
+    bool any = false;
+    float closest = tmax;
+    if (COUNT) prim_tests += (unsigned)count;
+    for (int i = begin; i < begin + count; ++i) {
+        PrimHead p = load_head(S.prims, i);
+        float t;
+        bool h = (p.type == RTOW_PRIM_MEDIUM) ? medium_t(S, i, p, r, tmin, closest, g, visit, t) : simple_prim_t(S, i, p, r, tmin, closest, t);
+        if (h) { any = true; closest = t; t_out = t; prim_out = i; }
+    }
+    return any;
+}
+
+// ---- closest hit, EXACT: the reference tree as is -- box test, then BOTH children with the
+// same un-narrowed (tmin,tmax) (bvhNode.h:66-96).  Stackless walk of the threaded entries. ------
+template <bool COUNT>
+__device__ __forceinline__ bool closest_hit_exact(const DScene &S, const Ray &r, float tmin, float tmax, const Rng *g, float &t_out, int &prim_out,
+                                                  unsigned &node_visits, unsigned &prim_tests) {
+    if (S.top_kind != RTOW_TOP_BVH) return run_hit<COUNT>(S, 0, S.n_prims_top, r, tmin, tmax, g, 0, t_out, prim_out, prim_tests);
+    float best = __int_as_float(0x7f800000);
+    int best_prim = -1;
+    int i = 0;
+    const int n = S.n_entries;
+    while (i < n) {
+        float4 a = __ldg(&S.entries[2 * i]);
+        float4 b = __ldg(&S.entries[2 * i + 1]);
+        int kind = __float_as_int(b.w);
+        if (kind == ENTRY_NODE) {
+            if (COUNT) node_visits++;
+            i = aabb_hit(a.x, a.y, a.z, b.x, b.y, b.z, r, tmin, tmax) ? i + 1 : __float_as_int(a.w);
+        } else {
+            float t; int pid; bool h;
+            if (kind == ENTRY_SPHERE) {
+                if (COUNT) prim_tests++;
+                pid = __float_as_int(b.x);
+                h = sphere_t(a.x, a.y, a.z, a.w, r, tmin, tmax, t);
+            } else {
+                int4 o = __ldg(&S.objects[__float_as_int(b.x)]);
+                h = run_hit<COUNT>(S, o.x, o.y, r, tmin, tmax, g, __float_as_int(b.y), t, pid, prim_tests);
+            }
+            if (h && t <= best) { best = t; best_prim = pid; }
+            i++;
+        }
+    }
+    if (best_prim < 0) return false;
+    t_out = best; prim_out = best_prim;
+    return true;
+}
+
+// ---- hit record of the winning primitive (recomputed from t with the hit code's arithmetic) ----
+// mathUtilities.h:62-68: the two affine maps run in double (M_PI), narrowed on assignment
+__device__ __forceinline__ void sphere_uv(float px, float py, float pz, float &u, float &v) {
+    const double PI = 3.14159265358979323846;
+    float phi = atan2f(pz, px);
+    float theta = asinf(py);
+    u = (float)(1 - ((double)phi + PI) / (2 * PI));
+    v = (float)(((double)theta + PI / 2) / PI);
+}
+
+struct Hit {
+    float t, u, v;
+    float p[3], n[3];
+    int prim, mat;
+};
+
+// r is the ray in the root aggregate's space (after the root chain).  want_uv: sphere (u,v)
+// costs atan2f+asinf and only ImageTexture reads it (texture.h:65-79).
+__device__ __forceinline__ void prim_record(const DScene &S, int pid, const Ray &r_in, float t, bool want_uv, Hit &h) {
+    PrimHead p = load_head(S.prims, pid);
+    Ray r = r_in;
+    chain_ray(S.xforms, p.xf_begin, p.xf_count, r);
+    float pt[3] = {r.ox + t * r.dx, r.oy + t * r.dy, r.oz + t * r.dz};   // ray.h:10
+    float n[3] = {0.f, 0.f, 0.f};
+    float u = 0.f, v = 0.f;
+    const float4 *f = reinterpret_cast<const float4 *>(S.prims + pid * 5 + 1);
+    float4 f0 = __ldg(&f[0]);
+    if (p.type == RTOW_PRIM_SPHERE) {
+        n[0] = (pt[0] - f0.x) / f0.w; n[1] = (pt[1] - f0.y) / f0.w; n[2] = (pt[2] - f0.z) / f0.w;   // sphere.h:49-51
+        if (want_uv) sphere_uv(n[0], n[1], n[2], u, v);
+    } else if (p.type == RTOW_PRIM_MOVING_SPHERE) {                                                  // sphere.h:101-106
+        float4 f1 = __ldg(&f[1]), f2 = __ldg(&f[2]);
+        float cx, cy, cz;
+        moving_center(f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w, r.time, cx, cy, cz);
+        n[0] = (pt[0] - cx) / f2.x; n[1] = (pt[1] - cy) / f2.x; n[2] = (pt[2] - cz) / f2.x;
+    } else if (p.type == RTOW_PRIM_MEDIUM) {
+        n[0] = 1.f;                                                                                  // constantMedium.h:66
+    } else {
+        float x, y;
+        if (p.type == RTOW_PRIM_RECT_XY) { x = pt[0]; y = pt[1]; n[2] = 1.f; }
+        else if (p.type == RTOW_PRIM_RECT_XZ) { x = pt[0]; y = pt[2]; n[1] = 1.f; }
+        else { x = pt[1]; y = pt[2]; n[0] = 1.f; }
+        u = (x - f0.x) / (f0.y - f0.x);                                                              // xy_rect.h:33-34
+        v = (y - f0.z) / (f0.w - f0.z);
+    }
+    chain_hit(S.xforms, p.xf_begin, p.xf_count, pt, n);
+    chain_hit(S.xforms, S.root_xf_begin, S.root_xf_count, pt, n);
+    h.t = t; h.prim = pid; h.mat = p.mat_id; h.u = u; h.v = v;
+    h.p[0] = pt[0]; h.p[1] = pt[1]; h.p[2] = pt[2];
+    h.n[0] = n[0]; h.n[1] = n[1]; h.n[2] = n[2];
+}
+
+}  // namespace rtow
