@@ -267,6 +267,20 @@ int rtow_resolve_device(rtow_scene *scene, const float *d_accum, int32_t width, 
 int rtow_trace_counters(rtow_scene *scene, const rtow_ray *rays, uint64_t n, int traverse,
                         double *node_visits_per_ray, double *prim_tests_per_ray);
 
+/* Work counters of one render (counting build of the render kernel): what the roofline's
+ * algorithmic-work figure is computed from (ops_per_ray = 27*V + sum P*F + shade). */
+typedef struct rtow_work_counters {
+    uint64_t paths, rays;
+    double node_visits_per_ray;    /* EXACT: slab tests; FAST: 4-wide node visits (4 child boxes each) */
+    double prim_tests_per_ray;
+    double noise_evals_per_ray, checker_evals_per_ray, image_evals_per_ray;
+    double scatters_per_ray;
+    int32_t traverse;              /* the traversal that was counted (RTOW_TRAVERSE_*) */
+    int32_t reserved;
+} rtow_work_counters;
+int rtow_render_counters(rtow_scene *scene, const rtow_camera *cam, const rtow_render_params *params,
+                         rtow_work_counters *out);
+
 const char *rtow_last_error(void);
 const char *rtow_build_info(void);
 

@@ -91,8 +91,8 @@ std::string g_error;
 std::string g_image_dir = ".";
 
 struct MuteCout {   // Camera's constructor prints its matrices (camera.h:96-106)
+    std::ostringstream sink;   // declared (hence constructed) before `old`, whose initialiser uses it
     std::streambuf *old;
-    std::ostringstream sink;
     MuteCout() : old(std::cout.rdbuf(sink.rdbuf())) {}
     ~MuteCout() { std::cout.rdbuf(old); }
 };

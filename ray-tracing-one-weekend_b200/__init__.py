@@ -9,6 +9,7 @@ The directory name carries a hyphen (it is the repository's package directory), 
 loaded under the module name ``rtow_b200`` by ``__graft_entry__.load_package()``.
 """
 from . import _abi as abi  # noqa: F401
+from . import raysets  # noqa: F401
 from .binding import (  # noqa: F401
     RtowError,
     lib,

@@ -125,6 +125,21 @@ class Stats(C.Structure):
     ]
 
 
+class WorkCounters(C.Structure):
+    _fields_ = [
+        ("paths", C.c_uint64),
+        ("rays", C.c_uint64),
+        ("node_visits_per_ray", C.c_double),
+        ("prim_tests_per_ray", C.c_double),
+        ("noise_evals_per_ray", C.c_double),
+        ("checker_evals_per_ray", C.c_double),
+        ("image_evals_per_ray", C.c_double),
+        ("scatters_per_ray", C.c_double),
+        ("traverse", C.c_int32),
+        ("reserved", C.c_int32),
+    ]
+
+
 def default_render_params(width, height, spp, seed=1, max_depth=50, kernel=KERNEL_AUTO, traverse=TRAVERSE_AUTO,
                           sample_begin=0, sample_count=0):
     """defines.h defaults: GLOBAL_ILLUM_EN 1, SKY_ILLUM_GAIN 1.0, GLOBAL_ILLUM_GAIN 0.3, DEPTH_RECURSION 50."""

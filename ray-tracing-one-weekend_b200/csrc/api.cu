@@ -354,8 +354,8 @@ int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out)
         }
     }
 
-    CUDA_TRY(cudaMalloc((void **)&s->d_counters, 4 * sizeof(unsigned long long)));
-    CUDA_TRY(cudaMemset(s->d_counters, 0, 4 * sizeof(unsigned long long)));
+    CUDA_TRY(cudaMalloc((void **)&s->d_counters, RTOW_N_COUNTERS * sizeof(unsigned long long)));
+    CUDA_TRY(cudaMemset(s->d_counters, 0, RTOW_N_COUNTERS * sizeof(unsigned long long)));
     CUDA_TRY(cudaEventCreate(&s->ev0));
     CUDA_TRY(cudaEventCreate(&s->ev1));
     CUDA_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
@@ -414,11 +414,11 @@ int rtow_trace_counters(rtow_scene *s, const rtow_ray *rays, uint64_t n, int tra
     CUDA_TRY(cudaSetDevice(s->device));
     if (int rc = ensure_ray_buffers(s, n)) return rc;
     cudaStream_t st = s->stream;
-    CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 4 * sizeof(unsigned long long), st));
+    CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTOW_N_COUNTERS * sizeof(unsigned long long), st));
     CUDA_TRY(cudaMemcpyAsync(s->d_rays, rays, n * sizeof(rtow_ray), cudaMemcpyHostToDevice, st));
     launch_trace(s->d, (const rtow_ray *)s->d_rays, n, (rtow_hit *)s->d_hits, trav, 0, s->d_counters, true, st);
     CUDA_TRY(cudaGetLastError());
-    unsigned long long c[4];
+    unsigned long long c[RTOW_N_COUNTERS];
     CUDA_TRY(cudaMemcpyAsync(c, s->d_counters, sizeof c, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     if (node_visits_per_ray) *node_visits_per_ray = (double)c[2] / (double)n;
@@ -432,13 +432,38 @@ int rtow_render_accumulate_device(rtow_scene *s, const rtow_camera *cam, const r
     if (!d_accum) return set_error(RTOW_ERR_INVALID_ARG, "rtow_render_accumulate_device: null accumulator");
     CUDA_TRY(cudaSetDevice(s->device));
     cudaStream_t st = (cudaStream_t)stream;
-    CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 4 * sizeof(unsigned long long), st));
+    CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTOW_N_COUNTERS * sizeof(unsigned long long), st));
     CUDA_TRY(cudaEventRecord(s->ev0, st));
-    launch_render_mega(s->d, *cam, L, d_accum, s->d_counters, st);
+    launch_render_mega(s->d, *cam, L, d_accum, s->d_counters, false, st);
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaEventRecord(s->ev1, st));
     s->pending = true;
     s->pending_launches = 1;
+    return RTOW_OK;
+}
+
+int rtow_render_counters(rtow_scene *s, const rtow_camera *cam, const rtow_render_params *params, rtow_work_counters *out) {
+    RenderLaunch L;
+    if (int rc = check_render_args(s, cam, params, &L)) return rc;
+    if (!out) return set_error(RTOW_ERR_INVALID_ARG, "rtow_render_counters: null output");
+    std::memset(out, 0, sizeof *out);
+    CUDA_TRY(cudaSetDevice(s->device));
+    size_t pixels = (size_t)params->width * params->height;
+    if (int rc = ensure_image_buffers(s, pixels)) return rc;
+    cudaStream_t st = s->stream;
+    CUDA_TRY(cudaMemsetAsync(s->d_accum, 0, pixels * 3 * sizeof(float), st));
+    CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTOW_N_COUNTERS * sizeof(unsigned long long), st));
+    launch_render_mega(s->d, *cam, L, s->d_accum, s->d_counters, true, st);
+    CUDA_TRY(cudaGetLastError());
+    unsigned long long c[RTOW_N_COUNTERS];
+    CUDA_TRY(cudaMemcpyAsync(c, s->d_counters, sizeof c, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    double rays = c[0] ? (double)c[0] : 1.0;
+    out->paths = c[1]; out->rays = c[0];
+    out->node_visits_per_ray = c[2] / rays; out->prim_tests_per_ray = c[3] / rays;
+    out->noise_evals_per_ray = c[4] / rays; out->checker_evals_per_ray = c[5] / rays;
+    out->image_evals_per_ray = c[6] / rays; out->scatters_per_ray = c[7] / rays;
+    out->traverse = L.traverse;
     return RTOW_OK;
 }
 
@@ -448,7 +473,7 @@ int rtow_stream_stats(rtow_scene *s, void *stream, rtow_stats *stats) {
     CUDA_TRY(cudaSetDevice(s->device));
     CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
     if (!s->pending) return RTOW_OK;
-    unsigned long long c[4];
+    unsigned long long c[RTOW_N_COUNTERS];
     CUDA_TRY(cudaMemcpy(c, s->d_counters, sizeof c, cudaMemcpyDeviceToHost));
     stats->rays = c[0]; stats->paths = c[1];
     CUDA_TRY(cudaEventElapsedTime(&stats->kernel_ms, s->ev0, s->ev1));

@@ -75,6 +75,7 @@ void launch_trace(const DScene &S, const rtow_ray *d_rays, uint64_t n, rtow_hit 
 // persistent path tracer: when its path ends it starts its next sample at once (the bounce loop
 // is flat), so lanes of a warp stay busy until their own sample list is exhausted.  Partial sums
 // are combined with shuffles in a fixed order -> the image is deterministic for a seed.
+template <bool COUNT>
 __global__ void __launch_bounds__(256) render_mega_kernel(DScene S, rtow_camera cam, RenderLaunch L, float *__restrict__ accum,
                                                           unsigned long long *__restrict__ counters) {
     __shared__ PerlinSmem perlin;
@@ -96,6 +97,7 @@ __global__ void __launch_bounds__(256) render_mega_kernel(DScene S, rtow_camera 
     float acc[3] = {0.f, 0.f, 0.f};
     unsigned long long rays = 0, paths = 0;
     unsigned nv = 0, pt = 0;
+    unsigned c_noise = 0, c_checker = 0, c_image = 0, c_scatter = 0;   // COUNT build only
 
     int s = lane_s - Sl;                                      // next sample index (relative) = s + Sl
     bool alive = false;
@@ -125,7 +127,7 @@ __global__ void __launch_bounds__(256) render_mega_kernel(DScene S, rtow_camera 
         Ray rl = r;
         chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, rl);
         float t; int pid;
-        if (!closest_hit<false>(S, L.traverse, rl, 0.001f, FLT_MAX, &g, t, pid, nv, pt)) {
+        if (!closest_hit<COUNT>(S, L.traverse, rl, 0.001f, FLT_MAX, &g, t, pid, nv, pt)) {
             if (L.global_illum_en) {
                 if (depth < 1) {                                              // color.h:35-50
                     float ux, uy, uz;
@@ -147,6 +149,13 @@ __global__ void __launch_bounds__(256) render_mega_kernel(DScene S, rtow_camera 
                 float atten[3], sd[3], st;
                 float rd[3] = {r.dx, r.dy, r.dz};
                 bool go = scatter(S, &perlin, m, h, rd, r.time, g, atten, sd, st, em);
+                if (COUNT) {
+                    c_scatter++;
+                    if (m.type != RTOW_MAT_METAL && m.type != RTOW_MAT_DIELECTRIC) {
+                        int tt = __ldg(&S.textures[2 * m.tex]).x;
+                        c_noise += tt == RTOW_TEX_NOISE; c_checker += tt == RTOW_TEX_CHECKER; c_image += tt == RTOW_TEX_IMAGE;
+                    }
+                }
                 Lr[0] += T[0] * em[0]; Lr[1] += T[1] * em[1]; Lr[2] += T[2] * em[2];
                 if (go) {
                     T[0] *= atten[0]; T[1] *= atten[1]; T[2] *= atten[2];
@@ -187,15 +196,25 @@ __global__ void __launch_bounds__(256) render_mega_kernel(DScene S, rtow_camera 
         atomicAdd(&counters[0], rays);
         atomicAdd(&counters[1], paths);
     }
+    if (COUNT) {
+        unsigned v[6] = {nv, pt, c_noise, c_checker, c_image, c_scatter};
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            unsigned long long x = v[k];
+            for (int off = 16; off; off >>= 1) x += __shfl_down_sync(0xffffffffu, x, off);
+            if (lane == 0) atomicAdd(&counters[2 + k], x);
+        }
+    }
 }
 
 void launch_render_mega(const DScene &S, const rtow_camera &cam, const RenderLaunch &L, float *d_accum,
-                        unsigned long long *d_counters, cudaStream_t stream) {
+                        unsigned long long *d_counters, bool count, cudaStream_t stream) {
     long long n_pixels = (long long)L.width * L.height;
     int ppw = 32 / L.lanes_per_pixel;
     long long warps = (n_pixels + ppw - 1) / ppw;
     long long blocks = (warps + 7) / 8;
-    render_mega_kernel<<<(unsigned)blocks, 256, 0, stream>>>(S, cam, L, d_accum, d_counters);
+    if (count) render_mega_kernel<true><<<(unsigned)blocks, 256, 0, stream>>>(S, cam, L, d_accum, d_counters);
+    else render_mega_kernel<false><<<(unsigned)blocks, 256, 0, stream>>>(S, cam, L, d_accum, d_counters);
 }
 
 // ---- resolve: main.cpp:955-989 -------------------------------------------------------------
