@@ -365,6 +365,28 @@ int ref_material_scatter(void *h, int mat_id, const rtow_ray *rin, const rtow_hi
     return ok;
 }
 
+// ImageTexture::value (texture.h:65-79) on caller-supplied RGB8 texels (the scene builders only
+// construct ImageTextures from files; this probe lets a small committed image pin the lookup).
+void ref_image_texture_value(const unsigned char *rgb8, int nx, int ny, const float *uv, uint64_t n, float *rgb) {
+    ImageTexture t(const_cast<unsigned char *>(rgb8), nx, ny);
+    for (uint64_t i = 0; i < n; ++i) {
+        vec3 c = t.value(uv[2 * i], uv[2 * i + 1], vec3(0, 0, 0));
+        rgb[3 * i] = c[0]; rgb[3 * i + 1] = c[1]; rgb[3 * i + 2] = c[2];
+    }
+}
+// reflect / refract / schlick of material.h:11-32 on n inputs (v, n, ni_over_nt | cosine, refIndex).
+void ref_reflect_refract(const float *v, const float *nrm, const float *ni, uint64_t n, float *refl, float *refr, int *ok) {
+    for (uint64_t i = 0; i < n; ++i) {
+        vec3 a(v[3 * i], v[3 * i + 1], v[3 * i + 2]), b(nrm[3 * i], nrm[3 * i + 1], nrm[3 * i + 2]);
+        vec3 r = reflect(a, b), q(0, 0, 0);
+        ok[i] = refract(a, b, ni[i], q) ? 1 : 0;
+        for (int k = 0; k < 3; ++k) { refl[3 * i + k] = r[k]; refr[3 * i + k] = q[k]; }
+    }
+}
+void ref_schlick(const float *cosine, const float *ri, uint64_t n, float *out) {
+    for (uint64_t i = 0; i < n; ++i) out[i] = schlick(cosine[i], ri[i]);
+}
+
 // stb_image decode exactly as scenes.h:47,140 calls it (3-channel JPEGs; req_comp 0).
 unsigned char *ref_decode_image(const char *path, int *nx, int *ny, int *nn) { return stbi_load(path, nx, ny, nn, 0); }
 void ref_free_image(unsigned char *p) { stbi_image_free(p); }
