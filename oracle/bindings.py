@@ -149,6 +149,9 @@ class RefOracle:
         L.ref_sphere_uv.argtypes = [vp, u64, vp]
         L.ref_material_scatter.restype = C.c_int
         L.ref_material_scatter.argtypes = [vp, C.c_int, vp, vp, u64, C.c_float * 3, vp, C.c_float * 3]
+        L.ref_image_texture_value.argtypes = [vp, C.c_int, C.c_int, vp, u64, vp]
+        L.ref_reflect_refract.argtypes = [vp, vp, vp, u64, vp, vp, vp]
+        L.ref_schlick.argtypes = [vp, vp, u64, vp]
         L.ref_decode_image.restype = C.POINTER(C.c_uint8)
         L.ref_decode_image.argtypes = [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.ref_free_image.argtypes = [C.POINTER(C.c_uint8)]
@@ -202,6 +205,28 @@ class RefOracle:
         self.L.ref_sphere_uv(_ptr(p), len(p), _ptr(out))
         return out
 
+    def image_texture_value(self, image, uv):
+        """ImageTexture::value (texture.h:65-79) on caller-supplied RGB8 texels."""
+        img = np.ascontiguousarray(image, dtype=np.uint8)
+        uv = np.ascontiguousarray(uv, dtype=np.float32)
+        out = np.zeros((len(uv), 3), dtype=np.float32)
+        self.L.ref_image_texture_value(_ptr(img), img.shape[1], img.shape[0], _ptr(uv), len(uv), _ptr(out))
+        return out
+
+    def reflect_refract(self, v, n, ni):
+        """material.h:11-26 -> (reflected, refracted, refract_ok)"""
+        v = np.ascontiguousarray(v, dtype=np.float32); n = np.ascontiguousarray(n, dtype=np.float32)
+        ni = np.ascontiguousarray(ni, dtype=np.float32)
+        refl = np.zeros_like(v); refr = np.zeros_like(v); ok = np.zeros(len(v), dtype=np.int32)
+        self.L.ref_reflect_refract(_ptr(v), _ptr(n), _ptr(ni), len(v), _ptr(refl), _ptr(refr), _ptr(ok))
+        return refl, refr, ok
+
+    def schlick(self, cosine, ri):
+        cosine = np.ascontiguousarray(cosine, dtype=np.float32); ri = np.ascontiguousarray(ri, dtype=np.float32)
+        out = np.zeros(len(cosine), dtype=np.float32)
+        self.L.ref_schlick(_ptr(cosine), _ptr(ri), len(cosine), _ptr(out))
+        return out
+
     def tonemap_bgra8(self, mean_rgb):
         mean_rgb = np.ascontiguousarray(mean_rgb, dtype=np.float32)
         H, W = mean_rgb.shape[:2]
@@ -244,7 +269,35 @@ class PortOracle:
         L.rtow_oracle_camera_ray.argtypes = [C.POINTER(abi.Camera), C.c_float, C.c_float, u64, vp]
         L.rtow_oracle_scatter_fixed.restype = C.c_int
         L.rtow_oracle_scatter_fixed.argtypes = [SD, vp, vp, u64, C.c_float * 3, vp, C.c_float * 3]
+        f3 = C.c_float * 3
+        L.rtow_oracle_reflect.argtypes = [f3, f3, f3]
+        L.rtow_oracle_refract.restype = C.c_int
+        L.rtow_oracle_refract.argtypes = [f3, f3, C.c_float, f3]
+        L.rtow_oracle_schlick.restype = C.c_float
+        L.rtow_oracle_schlick.argtypes = [C.c_float, C.c_float]
+        L.rtow_oracle_resolve.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp]
         self.L = L
+
+    def reflect_refract(self, v, n, ni):
+        f3 = C.c_float * 3
+        v = np.asarray(v, dtype=np.float32); n = np.asarray(n, dtype=np.float32)
+        refl = np.zeros_like(v); refr = np.zeros_like(v); ok = np.zeros(len(v), dtype=np.int32)
+        o = f3()
+        for i in range(len(v)):
+            self.L.rtow_oracle_reflect(f3(*v[i]), f3(*n[i]), o); refl[i] = o[:]
+            ok[i] = self.L.rtow_oracle_refract(f3(*v[i]), f3(*n[i]), float(ni[i]), o); refr[i] = o[:]
+        return refl, refr, ok
+
+    def schlick(self, cosine, ri):
+        return np.array([self.L.rtow_oracle_schlick(float(c), float(r)) for c, r in zip(cosine, ri)], dtype=np.float32)
+
+    def resolve(self, sum_rgb, spp, want_bgra=True):
+        sum_rgb = np.ascontiguousarray(sum_rgb, dtype=np.float32)
+        H, W = sum_rgb.shape[:2]
+        mean = np.zeros((H, W, 3), dtype=np.float32)
+        bgra = np.zeros((H, W, 4), dtype=np.uint8)
+        self.L.rtow_oracle_resolve(_ptr(sum_rgb), W, H, spp, _ptr(mean), _ptr(bgra))
+        return mean, bgra
 
     def philox(self, ctr, key):
         out = (C.c_uint32 * 4)()

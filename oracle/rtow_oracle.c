@@ -589,3 +589,30 @@ int rtow_oracle_scatter_fixed(const rtow_scene_desc *s, const rtow_hit *h, const
     memcpy(scattered->o, so, sizeof so); memcpy(scattered->d, sd, sizeof sd); scattered->time = st;
     return go;
 }
+
+/* material.h:11-32 on single inputs, for the per-function tests. */
+void rtow_oracle_reflect(const float v[3], const float n[3], float out[3]) { reflect3(v, n, out); }
+int rtow_oracle_refract(const float v[3], const float n[3], float ni, float out[3]) {
+    out[0] = out[1] = out[2] = 0.f;
+    return refract3(v, n, ni, out);
+}
+float rtow_oracle_schlick(float cosine, float ri) { return schlick(cosine, ri); }
+
+/* main.cpp:955-989: sums over `spp` samples -> mean (multiply by float(1.0/spp), vec3.h:133-139), sqrt tone
+ * curve, 255.99 scale in double, uint16 truncation, clamp 255, store B,G,R,0.  Either output may be NULL. */
+void rtow_oracle_resolve(const float *sum_rgb, int width, int height, int spp, float *mean_rgb, uint8_t *bgra8) {
+    float k = (float)(1.0 / (float)spp);
+    for (size_t p = 0; p < (size_t)width * height; ++p) {
+        float c[3];
+        for (int i = 0; i < 3; ++i) { c[i] = sum_rgb[3 * p + i] * k; if (mean_rgb) mean_rgb[3 * p + i] = c[i]; }
+        if (bgra8) {
+            unsigned q[3];
+            for (int i = 0; i < 3; ++i) {
+                double sc = 255.99 * sqrtf(c[i]);
+                uint16_t v = (uint16_t)(int)(sc < 65535.0 ? (sc > 0.0 ? sc : 0.0) : 65535.0);
+                q[i] = v > 255 ? 255u : v;
+            }
+            bgra8[4 * p + 0] = (uint8_t)q[2]; bgra8[4 * p + 1] = (uint8_t)q[1]; bgra8[4 * p + 2] = (uint8_t)q[0]; bgra8[4 * p + 3] = 0;
+        }
+    }
+}

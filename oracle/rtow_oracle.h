@@ -19,6 +19,10 @@ int rtow_oracle_render(const rtow_scene_desc *s, const rtow_camera *cam, const r
 void rtow_oracle_camera_ray(const rtow_camera *cam, float s, float t, uint64_t seed, rtow_ray *out);
 int rtow_oracle_scatter_fixed(const rtow_scene_desc *s, const rtow_hit *h, const rtow_ray *rin, uint64_t seed,
                               float atten[3], rtow_ray *scattered, float emitted[3]);
+void rtow_oracle_reflect(const float v[3], const float n[3], float out[3]);
+int rtow_oracle_refract(const float v[3], const float n[3], float ni, float out[3]);
+float rtow_oracle_schlick(float cosine, float ri);
+void rtow_oracle_resolve(const float *sum_rgb, int width, int height, int spp, float *mean_rgb, uint8_t *bgra8);
 #ifdef __cplusplus
 }
 #endif
