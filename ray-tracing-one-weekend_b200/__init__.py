@@ -10,6 +10,7 @@ loaded under the module name ``rtow_b200`` by ``__graft_entry__.load_package()``
 """
 from . import _abi as abi  # noqa: F401
 from . import raysets  # noqa: F401
+from . import sharding  # noqa: F401
 from .binding import (  # noqa: F401
     RtowError,
     lib,
