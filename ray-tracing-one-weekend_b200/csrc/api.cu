@@ -349,7 +349,8 @@ int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out)
             D.scene_radius = fb.radius;
             D.fast_time_lo = fb.time_lo; D.fast_time_hi = fb.time_hi;
             if ((rc = upload(s, fb.nodes.data(), fb.nodes.size(), &D.fast_nodes))) return rc;
-            if ((rc = upload(s, fb.leaves.data(), fb.leaves.size(), &D.fast_leaves))) return rc;
+            if ((rc = upload(s, fb.spheres.data(), fb.spheres.size(), &D.fast_spheres))) return rc;
+            if ((rc = upload(s, fb.guards.data(), fb.guards.size(), &D.fast_guards))) return rc;
             s->has_fast = true;
         }
     }

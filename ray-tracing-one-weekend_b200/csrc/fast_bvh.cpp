@@ -210,7 +210,10 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
         if (nd.right < 0 && nd.right != nd.left) { if (owner[~nd.right] >= 0) return fail("object referenced by two nodes"); owner[~nd.right] = i; }
         if (nd.left < 0 && nd.right == nd.left) twice[~nd.left] = 1;
     }
-    out.leaves.assign((size_t)n * FAST_LEAF_F4, make_float4(0, 0, 0, 0));
+    if (n > FAST_LEAF_ID_MASK) return fail("too many objects for the leaf reference encoding");
+    out.spheres.assign((size_t)n, make_float4(0, 0, 0, 0));
+    out.guards.assign((size_t)n * 2, make_float4(0, 0, 0, 0));
+    std::vector<int32_t> leaf_ref(n);
     for (int o = 0; o < n; ++o) {
         if (owner[o] < 0) return fail("object not referenced by the tree");
         const rtow_bvh_node &g = d->nodes[owner[o]];
@@ -219,11 +222,13 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
         bool simple = ob.prim_count == 1 && p0.type == RTOW_PRIM_SPHERE && p0.xform_count == 0;
         bool has_medium = false;
         for (int p = ob.prim_begin; p < ob.prim_begin + ob.prim_count; ++p) has_medium |= d->prims[p].type == RTOW_PRIM_MEDIUM;
-        int kind = simple ? 1 : 0;   // ENTRY_SPHERE / ENTRY_OBJECT
-        if (twice[o] && has_medium) kind |= FAST_LEAF_TWICE;
-        out.leaves[(size_t)o * 3 + 0] = make_float4(g.bmin[0], g.bmin[1], g.bmin[2], i2f(o));
-        out.leaves[(size_t)o * 3 + 1] = make_float4(g.bmax[0], g.bmax[1], g.bmax[2], i2f(kind));
-        if (simple) out.leaves[(size_t)o * 3 + 2] = make_float4(p0.f[0], p0.f[1], p0.f[2], p0.f[3]);
+        int32_t code = o;
+        if (simple) code |= FAST_LEAF_SPHERE;
+        if (twice[o] && has_medium) code |= FAST_LEAF_TWICE;
+        leaf_ref[o] = ~code;
+        out.guards[(size_t)o * 2 + 0] = make_float4(g.bmin[0], g.bmin[1], g.bmin[2], 0.f);
+        out.guards[(size_t)o * 2 + 1] = make_float4(g.bmax[0], g.bmax[1], g.bmax[2], 0.f);
+        if (simple) out.spheres[o] = make_float4(p0.f[0], p0.f[1], p0.f[2], p0.f[3]);
     }
 
     Builder B(boxes);
@@ -282,7 +287,7 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
                 set_lane(nd[2 * a], k, down(c.box.lo[a], pad));
                 set_lane(nd[2 * a + 1], k, up(c.box.hi[a], pad));
             }
-            if (c.obj >= 0) set_lane(nd[6], k, i2f(~c.obj));
+            if (c.obj >= 0) set_lane(nd[6], k, i2f(leaf_ref[c.obj]));
             else stack.push_back({kids[k], id, k, it.depth + 1});
         }
     }

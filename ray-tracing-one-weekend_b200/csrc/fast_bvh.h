@@ -22,15 +22,24 @@ namespace rtow {
 
 // Node = 8 x float4 (128 B, one cache line):
 //   [0] lo.x of the 4 children  [1] hi.x  [2] lo.y  [3] hi.y  [4] lo.z  [5] hi.z
-//   [6] child refs as int bits: >= 0 node index, < 0 leaf = ~ref, FAST_EMPTY = no child
+//   [6] child refs as int bits: >= 0 node index; < 0 leaf, ~ref = object id | FAST_LEAF_* flags;
+//       FAST_EMPTY = no child
 //   [7] unused
-enum { FAST_NODE_F4 = 8, FAST_LEAF_F4 = 3 };
+// Per object (leaf), indexed by object id:
+//   spheres[obj]        {cx,cy,cz,r} of a bare Sphere leaf (FAST_LEAF_SPHERE), else zeros
+//   guards[2*obj..+1]   {bmin.xyz, -} {bmax.xyz, -}: box of the reference BvhNode that owns the leaf
+enum { FAST_NODE_F4 = 8 };
 static const int32_t FAST_EMPTY = 0x7fffffff;
-enum { FAST_LEAF_TWICE = 0x100 };   // ORed into the leaf kind: n==1 node, evaluate a medium twice
+enum {
+    FAST_LEAF_SPHERE = 1 << 30,   // the object is one untransformed Sphere: test spheres[obj] directly
+    FAST_LEAF_TWICE = 1 << 29,    // n==1 node holding a medium: the reference evaluates it twice (bvhNode.h:38-40,70-71)
+    FAST_LEAF_ID_MASK = (1 << 29) - 1
+};
 
 struct FastBvh {
     std::vector<float4> nodes;    // FAST_NODE_F4 per node
-    std::vector<float4> leaves;   // FAST_LEAF_F4 per object, indexed by object id
+    std::vector<float4> spheres;  // one per object
+    std::vector<float4> guards;   // two per object
     int32_t root = 0;
     float center[3] = {0, 0, 0};
     float radius = 0;             // bounds every primitive box and centre, from `center`

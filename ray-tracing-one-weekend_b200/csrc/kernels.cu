@@ -8,6 +8,9 @@
 #include "rt_shade.cuh"
 #include "rt_fast.cuh"
 
+#include <algorithm>
+#include <cstdlib>
+
 namespace rtow {
 
 template <bool COUNT>
@@ -62,9 +65,133 @@ __global__ void __launch_bounds__(256) trace_kernel(DScene S, const rtow_ray *__
     }
 }
 
+// ---- trace, persistent form (RTOW_TRAVERSE_FAST) -----------------------------------------------
+// Closest-hit trip counts vary by two orders of magnitude between rays (0 node visits for a ray that misses the
+// scene box, > 200 for one that grazes a million spheres), so one-thread-per-ray leaves most lanes of a warp idle
+// (ncu: 7-9 of 32 threads active per instruction).  Here a warp is persistent: lanes run the FastTrav state machine
+// in "while-while" form (descend nodes until a leaf, then test leaves together), and when fewer than
+// RTOW_REFILL_BELOW lanes are still traversing, the finished lanes write their hit records and fetch new rays
+// from a global counter.
+#define RTOW_REFILL_BELOW 24
+
+__device__ __forceinline__ void store_hit(rtow_hit *__restrict__ hits, uint64_t i, const DScene &S, const Ray &r, bool hit, float t, int pid) {
+    float4 o0, o1, o2;
+    if (hit) {
+        Hit h;
+        prim_record(S, pid, r, t, true, h);
+        o0 = make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.mat), h.n[0]);
+        o1 = make_float4(h.n[1], h.n[2], h.p[0], h.p[1]);
+        o2 = make_float4(h.p[2], h.u, h.v, 0.f);
+    } else {
+        o0 = make_float4(0.f, __int_as_float(-1), __int_as_float(-1), 0.f);
+        o1 = make_float4(0.f, 0.f, 0.f, 0.f);
+        o2 = o1;
+    }
+    float4 *out = reinterpret_cast<float4 *>(hits + i);
+    out[0] = o0; out[1] = o1; out[2] = o2;
+}
+
+template <bool COUNT, int MINB>
+__global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, const rtow_ray *__restrict__ rays, uint64_t n, rtow_hit *__restrict__ hits,
+                                                               uint64_t seed, unsigned long long *__restrict__ counters,
+                                                               unsigned long long *__restrict__ queue_head, int refill_below) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    int stack_ref[RTOW_FAST_STACK];
+    float stack_d[RTOW_FAST_STACK];
+    FastTrav T;
+    T.cur = RTOW_TRAV_DONE; T.sp = 0;
+    uint64_t idx = 0;
+    bool has_ray = false;
+    bool more = true;             // the queue may still hold rays
+    unsigned nv = 0, pt = 0;
+    Rng g;
+    rng_init(g, seed, 0, 0);
+
+    for (;;) {
+        // 1. finished lanes write their record
+        if (has_ray && T.cur == RTOW_TRAV_DONE) {
+            float t; int pid;
+            bool h = fast_result(S, T, t, pid);
+            store_hit(hits, idx, S, T.r, h, t, pid);
+            has_ray = false;
+        }
+        // 2. idle lanes fetch the next rays (consecutive indices for consecutive idle lanes)
+        if (more) {
+            const unsigned need = __ballot_sync(full, !has_ray);
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(queue_head, (unsigned long long)__popc(need));
+            base = __shfl_sync(full, base, 0);
+            if (base + __popc(need) >= n) more = false;
+            if (!has_ray) {
+                const uint64_t mine = base + __popc(need & ((1u << lane) - 1u));
+                if (mine < n) {
+                    idx = mine; has_ray = true;
+                    const float *q = reinterpret_cast<const float *>(rays + idx);
+                    Ray r;
+                    r.ox = __ldg(q + 0); r.oy = __ldg(q + 1); r.oz = __ldg(q + 2);
+                    r.dx = __ldg(q + 3); r.dy = __ldg(q + 4); r.dz = __ldg(q + 5);
+                    r.time = __ldg(q + 6);
+                    const float tmin = __ldg(q + 7), tmax = __ldg(q + 8);
+                    rng_init(g, seed, (uint32_t)idx, (uint32_t)(idx >> 32));
+                    chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, r);
+                    if (fast_covers(S, r, tmin, tmax)) {
+                        fast_begin(S, r, tmin, tmax, T);
+                    } else {
+                        // not covered by the culling argument: the reference walk, result parked in the state
+                        float t; int pid;
+                        T.r = r; T.tmin = tmin; T.tmax = tmax; T.best_obj = -1; T.best_prim = -1;
+                        if (closest_hit_exact<COUNT>(S, r, tmin, tmax, &g, t, pid, nv, pt)) { T.best = t; T.best_obj = 0; T.best_prim = pid; }
+                        T.cur = RTOW_TRAV_DONE;
+                    }
+                }
+            }
+        }
+        if (!__any_sync(full, has_ray)) break;
+        // 3. traverse until the warp runs low on active lanes (or, with the queue empty, until all are done)
+        for (;;) {
+            while (T.cur >= 0) fast_node<COUNT>(S, T, stack_ref, stack_d, nv);
+            if (T.cur != RTOW_TRAV_DONE) fast_leaf<COUNT>(S, T, &g, stack_ref, stack_d, pt);
+            const unsigned act = __ballot_sync(full, T.cur != RTOW_TRAV_DONE);
+            if (act == 0 || (more && __popc(act) < refill_below)) break;
+        }
+    }
+    if (COUNT) {
+        for (int off = 16; off; off >>= 1) {
+            nv += __shfl_down_sync(full, nv, off);
+            pt += __shfl_down_sync(full, pt, off);
+        }
+        if (lane == 0) {
+            atomicAdd(&counters[2], (unsigned long long)nv);
+            atomicAdd(&counters[3], (unsigned long long)pt);
+        }
+    }
+}
+
 void launch_trace(const DScene &S, const rtow_ray *d_rays, uint64_t n, rtow_hit *d_hits, int traverse, uint64_t seed,
                   unsigned long long *d_counters, bool count, cudaStream_t stream) {
     if (n == 0) return;
+    if (traverse == RTOW_TRAVERSE_FAST && S.fast_nodes) {
+        // persistent warps: enough blocks to fill every SM at the kernel's occupancy, never more warps than rays/32
+        unsigned long long *head = d_counters + RTOW_COUNTER_QUEUE_HEAD;
+        cudaMemsetAsync(head, 0, sizeof(unsigned long long), stream);
+        int dev = 0, sms = 148, per_sm = 4;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        static const int minb = [] { const char *e = getenv("RTOW_TRACE_MINB"); return e ? atoi(e) : 8; }();   // tuning knob (measured: 8 blocks/SM at 64 registers beats 4 at 124)
+        static const int refill = [] { const char *e = getenv("RTOW_TRACE_REFILL"); return e ? atoi(e) : RTOW_REFILL_BELOW; }();
+        auto go = [&](auto kern) {
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, 0);
+            unsigned long long want = (n + 127) / 128;
+            unsigned blocks = (unsigned)std::min<unsigned long long>(want, (unsigned long long)sms * (unsigned)std::max(per_sm, 1));
+            kern<<<blocks, 128, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters, head, refill);
+        };
+        if (count) go(trace_persistent_kernel<true, 4>);
+        else if (minb >= 8) go(trace_persistent_kernel<false, 8>);
+        else if (minb >= 6) go(trace_persistent_kernel<false, 6>);
+        else go(trace_persistent_kernel<false, 4>);
+        return;
+    }
     unsigned blocks = (unsigned)((n + 255) / 256);
     if (count) trace_kernel<true><<<blocks, 256, 0, stream>>>(S, d_rays, n, d_hits, traverse, seed, d_counters);
     else trace_kernel<false><<<blocks, 256, 0, stream>>>(S, d_rays, n, d_hits, traverse, seed, d_counters);

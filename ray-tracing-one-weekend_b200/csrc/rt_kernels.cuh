@@ -18,7 +18,8 @@ struct RenderLaunch {
 
 // counters (RTOW_N_COUNTERS u64): [0] rays (world->hit queries) [1] paths [2] node visits [3] prim tests
 // [4] noise-texture evals [5] checker evals [6] image evals [7] scatter calls   ([2..7]: counting builds only)
-enum { RTOW_N_COUNTERS = 8 };
+// [8] work-queue head of the persistent kernels
+enum { RTOW_N_COUNTERS = 16, RTOW_COUNTER_QUEUE_HEAD = 8 };
 void launch_trace(const DScene &S, const rtow_ray *d_rays, uint64_t n, rtow_hit *d_hits, int traverse, uint64_t seed,
                   unsigned long long *d_counters, bool count, cudaStream_t stream);
 void launch_render_mega(const DScene &S, const rtow_camera &cam, const RenderLaunch &L, float *d_accum,

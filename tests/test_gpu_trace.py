@@ -52,13 +52,14 @@ def test_bvh_stress_hits_match_oracle(gpu, abi, ob, port, n, mode):
     _compare(got, want, f"bvh_stress[{n}]/{mode}")
 
 
-def test_fast_equals_exact_on_large_bvh(gpu, abi, ob):
+@pytest.mark.parametrize("n_spheres,log2_rays", [(200000, 18), (1000000, 21)])
+def test_fast_equals_exact_on_large_bvh(gpu, abi, ob, n_spheres, log2_rays):
     """Size-independent property at a size the CPU oracle cannot sweep: the culled traversal of the
     rebuilt BVH returns exactly what the un-culled walk of the reference tree returns."""
-    host = gpu.HostScene("bvh_stress", seed=4242, n=200000)
+    host = gpu.HostScene("bvh_stress", seed=4242, n=n_spheres)
     dev = gpu.DeviceScene(host.desc)
     rays = np.concatenate([ob.coherent_rays(512), ob.coherent_rays(512, origin=(0.0, 0.0, -120.0)),
-                           ob.incoherent_rays(1 << 18, seed=5, extent=100.0)])
+                           ob.incoherent_rays(1 << log2_rays, seed=5, extent=100.0), ob.incoherent_rays(1 << (log2_rays - 2), seed=6, extent=300.0)])
     a, _ = dev.trace(rays, traverse=abi.TRAVERSE_EXACT)
     b, _ = dev.trace(rays, traverse=abi.TRAVERSE_FAST)
     assert (a["prim_id"] >= 0).mean() > 0.2
