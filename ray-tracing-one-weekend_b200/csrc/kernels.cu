@@ -73,47 +73,42 @@ __global__ void __launch_bounds__(256) trace_kernel(DScene S, const rtow_ray *__
 // RTOW_REFILL_BELOW lanes are still traversing, the finished lanes write their hit records and fetch new rays
 // from a global counter.
 #define RTOW_REFILL_BELOW 24
+#ifndef RTOW_TRACE_STACK_SMEM
+#define RTOW_TRACE_STACK_SMEM 12   // stack entries per lane kept in shared memory (4-warp block: 12 KB)
+#endif
 
-__device__ __forceinline__ void store_hit(rtow_hit *__restrict__ hits, uint64_t i, const DScene &S, const Ray &r, bool hit, float t, int pid) {
-    float4 o0, o1, o2;
-    if (hit) {
-        Hit h;
-        prim_record(S, pid, r, t, true, h);
-        o0 = make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.mat), h.n[0]);
-        o1 = make_float4(h.n[1], h.n[2], h.p[0], h.p[1]);
-        o2 = make_float4(h.p[2], h.u, h.v, 0.f);
-    } else {
-        o0 = make_float4(0.f, __int_as_float(-1), __int_as_float(-1), 0.f);
-        o1 = make_float4(0.f, 0.f, 0.f, 0.f);
-        o2 = o1;
-    }
-    float4 *out = reinterpret_cast<float4 *>(hits + i);
-    out[0] = o0; out[1] = o1; out[2] = o2;
-}
+// Kernel A writes {t, prim} into the first 8 bytes of each hit record (prim -1 = miss, RTOW_NEEDS_EXACT = the
+// culling argument does not cover this ray); kernel B (trace_finish_kernel, one thread per ray, coherent) runs the
+// reference walk for those few rays and expands every result to the full 48-byte record.  Keeping the record
+// arithmetic (divisions, atan2f/asinf) and the fallback walk out of the persistent loop halves its register need.
+#define RTOW_NEEDS_EXACT (-2)
 
 template <bool COUNT, int MINB>
 __global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, const rtow_ray *__restrict__ rays, uint64_t n, rtow_hit *__restrict__ hits,
                                                                uint64_t seed, unsigned long long *__restrict__ counters,
-                                                               unsigned long long *__restrict__ queue_head, int refill_below) {
+                                                               unsigned long long *__restrict__ queue_head, int refill_below, int leaf_min) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    int stack_ref[RTOW_FAST_STACK];
-    float stack_d[RTOW_FAST_STACK];
+    __shared__ int s_ref[RTOW_TRACE_STACK_SMEM * 128];
+    __shared__ float s_d[RTOW_TRACE_STACK_SMEM * 128];
+    SmemStack<RTOW_TRACE_STACK_SMEM> st;
+    st.sref = s_ref + (threadIdx.x >> 5) * (RTOW_TRACE_STACK_SMEM * 32) + lane;
+    st.sd = s_d + (threadIdx.x >> 5) * (RTOW_TRACE_STACK_SMEM * 32) + lane;
     FastTrav T;
     T.cur = RTOW_TRAV_DONE; T.sp = 0;
     uint64_t idx = 0;
     bool has_ray = false;
     bool more = true;             // the queue may still hold rays
     unsigned nv = 0, pt = 0;
-    Rng g;
-    rng_init(g, seed, 0, 0);
+    RngKey key;
+    key.seed = seed; key.pixel = key.sample = key.bounce = 0;
 
     for (;;) {
-        // 1. finished lanes write their record
+        // 1. finished lanes park their result
         if (has_ray && T.cur == RTOW_TRAV_DONE) {
-            float t; int pid;
-            bool h = fast_result(S, T, t, pid);
-            store_hit(hits, idx, S, T.r, h, t, pid);
+            float t = 0.f; int pid = -1;
+            if (!fast_result(S, T, t, pid)) pid = T.best_prim == RTOW_NEEDS_EXACT ? RTOW_NEEDS_EXACT : -1;
+            *reinterpret_cast<float2 *>(hits + idx) = make_float2(t, __int_as_float(pid));
             has_ray = false;
         }
         // 2. idle lanes fetch the next rays (consecutive indices for consecutive idle lanes)
@@ -133,27 +128,32 @@ __global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, c
                     r.dx = __ldg(q + 3); r.dy = __ldg(q + 4); r.dz = __ldg(q + 5);
                     r.time = __ldg(q + 6);
                     const float tmin = __ldg(q + 7), tmax = __ldg(q + 8);
-                    rng_init(g, seed, (uint32_t)idx, (uint32_t)(idx >> 32));
+                    key.pixel = (uint32_t)idx; key.sample = (uint32_t)(idx >> 32);
                     chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, r);
                     if (fast_covers(S, r, tmin, tmax)) {
                         fast_begin(S, r, tmin, tmax, T);
                     } else {
-                        // not covered by the culling argument: the reference walk, result parked in the state
-                        float t; int pid;
-                        T.r = r; T.tmin = tmin; T.tmax = tmax; T.best_obj = -1; T.best_prim = -1;
-                        if (closest_hit_exact<COUNT>(S, r, tmin, tmax, &g, t, pid, nv, pt)) { T.best = t; T.best_obj = 0; T.best_prim = pid; }
-                        T.cur = RTOW_TRAV_DONE;
+                        T.best_obj = -1; T.best_prim = RTOW_NEEDS_EXACT; T.cur = RTOW_TRAV_DONE;
                     }
                 }
             }
         }
         if (!__any_sync(full, has_ray)) break;
-        // 3. traverse until the warp runs low on active lanes (or, with the queue empty, until all are done)
+        // 3. traverse until the warp runs low on active lanes (or, with the queue empty, until all are done).
+        // Every round: lanes that need it pop one stack entry, then the warp votes and runs ONE kind of step --
+        // a 4-wide node step or a leaf test -- for the lanes that are at that kind; the others wait a round.
+        // Leaves are taken once `leaf_min` lanes wait at one (or nobody is at a node).
         for (;;) {
-            while (T.cur >= 0) fast_node<COUNT>(S, T, stack_ref, stack_d, nv);
-            if (T.cur != RTOW_TRAV_DONE) fast_leaf<COUNT>(S, T, &g, stack_ref, stack_d, pt);
-            const unsigned act = __ballot_sync(full, T.cur != RTOW_TRAV_DONE);
-            if (act == 0 || (more && __popc(act) < refill_below)) break;
+            fast_pop_one(T, st);
+            const bool at_node = fast_at_node(T), at_leaf = fast_at_leaf(T);
+            const unsigned mn = __ballot_sync(full, at_node), ml = __ballot_sync(full, at_leaf);
+            const unsigned alive = __ballot_sync(full, T.cur != RTOW_TRAV_DONE);
+            if (alive == 0 || (more && __popc(alive) < refill_below)) break;
+            if (ml == 0 || (mn != 0 && __popc(ml) < leaf_min)) {
+                if (at_node) fast_node<COUNT>(S, T, st, nv);
+            } else {
+                if (at_leaf) fast_leaf<COUNT>(S, T, key, pt);
+            }
         }
     }
     if (COUNT) {
@@ -162,6 +162,52 @@ __global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, c
             pt += __shfl_down_sync(full, pt, off);
         }
         if (lane == 0) {
+            atomicAdd(&counters[2], (unsigned long long)nv);
+            atomicAdd(&counters[3], (unsigned long long)pt);
+        }
+    }
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(256) trace_finish_kernel(DScene S, const rtow_ray *__restrict__ rays, uint64_t n, rtow_hit *__restrict__ hits,
+                                                           uint64_t seed, unsigned long long *__restrict__ counters) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned nv = 0, pt = 0;
+    if (i < n) {
+        const float *q = reinterpret_cast<const float *>(rays + i);
+        Ray r;
+        r.ox = __ldg(q + 0); r.oy = __ldg(q + 1); r.oz = __ldg(q + 2);
+        r.dx = __ldg(q + 3); r.dy = __ldg(q + 4); r.dz = __ldg(q + 5);
+        r.time = __ldg(q + 6);
+        chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, r);
+        const float2 res = *reinterpret_cast<const float2 *>(hits + i);
+        float t = res.x; int pid = __float_as_int(res.y);
+        if (pid == RTOW_NEEDS_EXACT) {
+            Rng g;
+            rng_init(g, seed, (uint32_t)i, (uint32_t)(i >> 32));
+            if (!closest_hit_exact<COUNT>(S, r, __ldg(q + 7), __ldg(q + 8), &g, t, pid, nv, pt)) pid = -1;
+        }
+        float4 o0, o1, o2;
+        if (pid >= 0) {
+            Hit h;
+            prim_record(S, pid, r, t, true, h);
+            o0 = make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.mat), h.n[0]);
+            o1 = make_float4(h.n[1], h.n[2], h.p[0], h.p[1]);
+            o2 = make_float4(h.p[2], h.u, h.v, 0.f);
+        } else {
+            o0 = make_float4(0.f, __int_as_float(-1), __int_as_float(-1), 0.f);
+            o1 = make_float4(0.f, 0.f, 0.f, 0.f);
+            o2 = o1;
+        }
+        float4 *out = reinterpret_cast<float4 *>(hits + i);
+        out[0] = o0; out[1] = o1; out[2] = o2;
+    }
+    if (COUNT) {
+        for (int off = 16; off; off >>= 1) {
+            nv += __shfl_down_sync(0xffffffffu, nv, off);
+            pt += __shfl_down_sync(0xffffffffu, pt, off);
+        }
+        if ((threadIdx.x & 31) == 0 && (nv | pt)) {
             atomicAdd(&counters[2], (unsigned long long)nv);
             atomicAdd(&counters[3], (unsigned long long)pt);
         }
@@ -178,17 +224,22 @@ void launch_trace(const DScene &S, const rtow_ray *d_rays, uint64_t n, rtow_hit 
         int dev = 0, sms = 148, per_sm = 4;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        static const int minb = [] { const char *e = getenv("RTOW_TRACE_MINB"); return e ? atoi(e) : 8; }();   // tuning knob (measured: 8 blocks/SM at 64 registers beats 4 at 124)
+        static const int minb = [] { const char *e = getenv("RTOW_TRACE_MINB"); return e ? atoi(e) : 5; }();   // tuning knob (measured on B200: 5 blocks/SM at 102 registers, no spills, beats 4, 6 and 8)
         static const int refill = [] { const char *e = getenv("RTOW_TRACE_REFILL"); return e ? atoi(e) : RTOW_REFILL_BELOW; }();
+        static const int leaf_min = [] { const char *e = getenv("RTOW_TRACE_LEAFMIN"); return e ? atoi(e) : 8; }();
         auto go = [&](auto kern) {
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, 0);
             unsigned long long want = (n + 127) / 128;
             unsigned blocks = (unsigned)std::min<unsigned long long>(want, (unsigned long long)sms * (unsigned)std::max(per_sm, 1));
-            kern<<<blocks, 128, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters, head, refill);
+            kern<<<blocks, 128, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters, head, refill, leaf_min);
+            unsigned fb = (unsigned)((n + 255) / 256);
+            if (count) trace_finish_kernel<true><<<fb, 256, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters);
+            else trace_finish_kernel<false><<<fb, 256, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters);
         };
         if (count) go(trace_persistent_kernel<true, 4>);
         else if (minb >= 8) go(trace_persistent_kernel<false, 8>);
         else if (minb >= 6) go(trace_persistent_kernel<false, 6>);
+        else if (minb >= 5) go(trace_persistent_kernel<false, 5>);
         else go(trace_persistent_kernel<false, 4>);
         return;
     }

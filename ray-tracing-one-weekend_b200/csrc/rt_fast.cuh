@@ -34,10 +34,21 @@ namespace rtow {
 
 #define RTOW_FAST_STACK 64
 #define RTOW_TRAV_DONE ((int)0x80000000)
+#define RTOW_TRAV_POP ((int)0x80000001)    // the lane must pop its stack before it can do a node or leaf step
 
 __device__ __forceinline__ float clamp_inv(float d) {
     float inv = 1.0f / d;
     return fabsf(inv) <= 1e30f ? inv : copysignf(1e30f, d);
+}
+
+// 32 B global load through the read-only path (LDG.E.256.CONSTANT); p must be 32-byte aligned
+__device__ __forceinline__ void ldg256(const float4 *p, float4 &a, float4 &b) {
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+}
+__device__ __forceinline__ float4 sel4(bool c, const float4 &a, const float4 &b) {
+    return make_float4(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z, c ? a.w : b.w);
 }
 
 __device__ __forceinline__ float lane4(const float4 &v, int k) { return k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w; }
@@ -49,7 +60,7 @@ __device__ __forceinline__ bool fast_covers(const DScene &S, const Ray &r, float
            fabsf(r.oy) <= 1e18f && fabsf(r.oz) <= 1e18f;
 }
 
-// Per-lane traversal state.  `cur`: >= 0 node, < 0 leaf reference, RTOW_TRAV_DONE finished.
+// Per-lane traversal state.  `cur`: >= 0 node, < 0 leaf reference, RTOW_TRAV_POP, RTOW_TRAV_DONE finished.
 struct FastTrav {
     Ray r;                      // in the root aggregate's space
     float tmin, tmax;
@@ -80,27 +91,54 @@ __device__ __forceinline__ void fast_begin(const DScene &S, const Ray &r, float 
     T.cur = S.fast_root; T.sp = 0;
 }
 
-// pop the next subtree that can still hold a hit with t <= best
-__device__ __forceinline__ void fast_pop(FastTrav &T, const int *stack_ref, const float *stack_d) {
-    const float ubp = T.bestc * 1.000001f;
-    int cur = RTOW_TRAV_DONE;
-    while (T.sp > 0) {
-        --T.sp;
-        if (stack_d[T.sp] <= ubp) { cur = stack_ref[T.sp]; break; }
+// Traversal stacks.  LocalStack lives in thread-local memory (an access with lanes at different depths costs one L1
+// wavefront per distinct depth).  SmemStack keeps the top CAP entries in shared memory, one 4-byte column per lane
+// (bank = lane: any mix of depths is one conflict-free wavefront), and only deeper entries in local memory.
+struct LocalStack {
+    int ref[RTOW_FAST_STACK];
+    float d[RTOW_FAST_STACK];
+    __device__ __forceinline__ void put(int i, int r, float dist) { ref[i] = r; d[i] = dist; }
+    __device__ __forceinline__ float dist(int i) const { return d[i]; }
+    __device__ __forceinline__ int node(int i) const { return ref[i]; }
+};
+template <int CAP>
+struct SmemStack {
+    int *sref;      // this lane's column: entry i at sref[i * 32]
+    float *sd;
+    int lref[RTOW_FAST_STACK - CAP];
+    float ld[RTOW_FAST_STACK - CAP];
+    __device__ __forceinline__ void put(int i, int r, float dist) {
+        if (i < CAP) { sref[i * 32] = r; sd[i * 32] = dist; } else { lref[i - CAP] = r; ld[i - CAP] = dist; }
     }
-    T.cur = cur;
+    __device__ __forceinline__ float dist(int i) const { return i < CAP ? sd[i * 32] : ld[i - CAP]; }
+    __device__ __forceinline__ int node(int i) const { return i < CAP ? sref[i * 32] : lref[i - CAP]; }
+};
+
+// One pop attempt: the next stacked subtree if it can still hold a hit with t <= best, else stay in POP state.
+// (One entry per call, so that a warp's lanes pop in lock-step instead of looping individually over stale entries.)
+template <class STACK>
+__device__ __forceinline__ void fast_pop_one(FastTrav &T, const STACK &st) {
+    if (T.cur != RTOW_TRAV_POP) return;
+    if (T.sp == 0) { T.cur = RTOW_TRAV_DONE; return; }
+    --T.sp;
+    if (st.dist(T.sp) <= T.bestc * 1.000001f) T.cur = st.node(T.sp);
 }
+__device__ __forceinline__ bool fast_at_node(const FastTrav &T) { return T.cur >= 0; }
+__device__ __forceinline__ bool fast_at_leaf(const FastTrav &T) { return T.cur < 0 && T.cur != RTOW_TRAV_DONE && T.cur != RTOW_TRAV_POP; }
 
 // One 4-wide node: cull the children, descend into the nearest, push the rest far-to-near.
-template <bool COUNT>
-__device__ __forceinline__ void fast_node(const DScene &S, FastTrav &T, int *stack_ref, float *stack_d, unsigned &node_visits) {
+template <bool COUNT, class STACK>
+__device__ __forceinline__ void fast_node(const DScene &S, FastTrav &T, STACK &st, unsigned &node_visits) {
     if (COUNT) node_visits++;
-    const int sx = T.ix < 0.f, sy = T.iy < 0.f, sz = T.iz < 0.f;
+    // A node is one 128 B line; a lane that is alone on its node pays one L1 wavefront per load instruction, so the
+    // line is fetched with four 256-bit loads (LDG.E.256, sm_100+) instead of seven 128-bit ones.
     const float4 *nd = S.fast_nodes + (size_t)T.cur * FAST_NODE_F4;
-    const float4 nx = __ldg(nd + sx), fx = __ldg(nd + (sx ^ 1));
-    const float4 ny = __ldg(nd + 2 + sy), fy = __ldg(nd + 2 + (sy ^ 1));
-    const float4 nz = __ldg(nd + 4 + sz), fz = __ldg(nd + 4 + (sz ^ 1));
-    const float4 rf = __ldg(nd + 6);
+    float4 lox, hix, loy, hiy, loz, hiz, rf, unused;
+    ldg256(nd, lox, hix); ldg256(nd + 2, loy, hiy); ldg256(nd + 4, loz, hiz); ldg256(nd + 6, rf, unused);
+    const bool sx = T.ix < 0.f, sy = T.iy < 0.f, sz = T.iz < 0.f;
+    const float4 nx = sel4(sx, hix, lox), fx = sel4(sx, lox, hix);
+    const float4 ny = sel4(sy, hiy, loy), fy = sel4(sy, loy, hiy);
+    const float4 nz = sel4(sz, hiz, loz), fz = sel4(sz, loz, hiz);
     const float aix = fabsf(T.ix), aiy = fabsf(T.iy), aiz = fabsf(T.iz);
     const float ub = T.bestc * 1.000001f;
     const float inf = __int_as_float(0x7f800000);
@@ -127,11 +165,10 @@ __device__ __forceinline__ void fast_node(const DScene &S, FastTrav &T, int *sta
     }
     RTOW_CSWAP(0, 1) RTOW_CSWAP(2, 3) RTOW_CSWAP(0, 2) RTOW_CSWAP(1, 3) RTOW_CSWAP(1, 2)
 #undef RTOW_CSWAP
-    if (d[3] < inf) { stack_ref[T.sp] = ref[3]; stack_d[T.sp] = d[3]; T.sp++; }
-    if (d[2] < inf) { stack_ref[T.sp] = ref[2]; stack_d[T.sp] = d[2]; T.sp++; }
-    if (d[1] < inf) { stack_ref[T.sp] = ref[1]; stack_d[T.sp] = d[1]; T.sp++; }
-    if (d[0] < inf) T.cur = ref[0];
-    else fast_pop(T, stack_ref, stack_d);
+    if (d[3] < inf) { st.put(T.sp, ref[3], d[3]); T.sp++; }
+    if (d[2] < inf) { st.put(T.sp, ref[2], d[2]); T.sp++; }
+    if (d[1] < inf) { st.put(T.sp, ref[1], d[1]); T.sp++; }
+    T.cur = d[0] < inf ? ref[0] : RTOW_TRAV_POP;
 }
 
 // A leaf that is not a bare sphere: a run of primitives (Box, MovingSphere, wrapped objects, media).  Kept out of line:
@@ -148,8 +185,14 @@ __device__ __noinline__ bool fast_object_leaf(const DScene &S, const Ray &r, flo
     return h;
 }
 
+// Where the per-path counter of a medium's free-flight draw comes from (rng_medium): built only if a medium is met.
+struct RngKey {
+    uint64_t seed;
+    uint32_t pixel, sample, bounce;
+};
+
 template <bool COUNT>
-__device__ __forceinline__ void fast_leaf(const DScene &S, FastTrav &T, const Rng *g, const int *stack_ref, const float *stack_d, unsigned &prim_tests) {
+__device__ __forceinline__ void fast_leaf(const DScene &S, FastTrav &T, const RngKey &key, unsigned &prim_tests) {
     const int code = ~T.cur;
     const int obj = code & FAST_LEAF_ID_MASK;
     float t = 0.f; int pid = -1; bool h;
@@ -158,7 +201,10 @@ __device__ __forceinline__ void fast_leaf(const DScene &S, FastTrav &T, const Rn
         const float4 sph = __ldg(S.fast_spheres + obj);
         h = sphere_t(sph.x, sph.y, sph.z, sph.w, T.r, T.tmin, T.tmax, t);
     } else {
-        h = fast_object_leaf<COUNT>(S, T.r, T.tmin, T.tmax, g, obj, code & FAST_LEAF_TWICE, t, pid, prim_tests);
+        Rng g;
+        rng_init(g, key.seed, key.pixel, key.sample);
+        g.bounce = key.bounce;
+        h = fast_object_leaf<COUNT>(S, T.r, T.tmin, T.tmax, &g, obj, code & FAST_LEAF_TWICE, t, pid, prim_tests);
     }
     if (h && (t < T.best || (t == T.best && obj > T.best_obj))) {
         const float4 g0 = __ldg(S.fast_guards + 2 * (size_t)obj), g1 = __ldg(S.fast_guards + 2 * (size_t)obj + 1);
@@ -168,7 +214,7 @@ __device__ __forceinline__ void fast_leaf(const DScene &S, FastTrav &T, const Rn
             T.eta = fminf(T.eta_g, fmaf(T.Kd, T.bestc, T.base));
         }
     }
-    fast_pop(T, stack_ref, stack_d);
+    T.cur = RTOW_TRAV_POP;
 }
 
 __device__ __forceinline__ bool fast_result(const DScene &S, const FastTrav &T, float &t_out, int &prim_out) {
@@ -183,13 +229,15 @@ template <bool COUNT>
 __device__ __forceinline__ bool closest_hit_fast(const DScene &S, const Ray &r, float tmin, float tmax, const Rng *g, float &t_out, int &prim_out,
                                                  unsigned &node_visits, unsigned &prim_tests) {
     if (!fast_covers(S, r, tmin, tmax)) return closest_hit_exact<COUNT>(S, r, tmin, tmax, g, t_out, prim_out, node_visits, prim_tests);
-    int stack_ref[RTOW_FAST_STACK];
-    float stack_d[RTOW_FAST_STACK];
+    LocalStack st;
     FastTrav T;
+    RngKey key;
+    key.seed = g ? ((uint64_t)g->k1 << 32 | g->k0) : 0; key.pixel = g ? g->pixel : 0; key.sample = g ? g->sample : 0; key.bounce = g ? g->bounce : 0;
     fast_begin(S, r, tmin, tmax, T);
     while (T.cur != RTOW_TRAV_DONE) {
-        while (T.cur >= 0) fast_node<COUNT>(S, T, stack_ref, stack_d, node_visits);
-        if (T.cur != RTOW_TRAV_DONE) fast_leaf<COUNT>(S, T, g, stack_ref, stack_d, prim_tests);
+        fast_pop_one(T, st);
+        if (fast_at_node(T)) fast_node<COUNT>(S, T, st, node_visits);
+        else if (fast_at_leaf(T)) fast_leaf<COUNT>(S, T, key, prim_tests);
     }
     return fast_result(S, T, t_out, prim_out);
 }
