@@ -197,8 +197,8 @@ def run_product(args):
     # spp sharding: rank g renders samples [b_g, b_g + n_g); the union is [0, spp) for any world size
     b = spp * rank // world
     n = spp * (rank + 1) // world - b
-    my = abi.default_render_params(W, H, spp, seed=RENDER_SEED, max_depth=DEPTH, sample_begin=b, sample_count=n, traverse=args.traverse)
-    full = abi.default_render_params(W, H, spp, seed=RENDER_SEED, max_depth=DEPTH, traverse=args.traverse)
+    my = abi.default_render_params(W, H, spp, seed=RENDER_SEED, max_depth=DEPTH, sample_begin=b, sample_count=n, traverse=args.traverse, kernel=args.kernel)
+    full = abi.default_render_params(W, H, spp, seed=RENDER_SEED, max_depth=DEPTH, traverse=args.traverse, kernel=args.kernel)
 
     accum = torch.zeros(H, W, 3, dtype=torch.float32, device=dev_t)
     rgb = torch.empty(H, W, 3, dtype=torch.float32, device=dev_t)
@@ -386,6 +386,7 @@ def main():
     ap.add_argument("--height", type=int, default=HEIGHT)
     ap.add_argument("--spp", type=int, default=SPP)
     ap.add_argument("--traverse", type=int, default=0, help="0 auto, 1 exact, 2 fast")
+    ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 megakernel, 2 wavefront")
     ap.add_argument("--no-bvh", action="store_true", help="skip the config-5 BVH hit-test figures")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--bvh-spheres", type=int, default=1000000)

@@ -3,6 +3,7 @@
 // There is no CPU path behind these symbols: without a CUDA device they return RTOW_ERR_NO_DEVICE.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -28,6 +29,12 @@ struct rtow_scene {
     float *d_accum = nullptr, *d_rgb = nullptr; uint8_t *d_bgra = nullptr; size_t img_cap = 0;
     cudaStream_t stream = nullptr;
     bool has_fast = false;
+    // wavefront path state (allocated on first use, regrown when the pool or the image grows)
+    WavefrontLaunch wf;
+    int wf_pool = 0; size_t wf_pixels = 0;
+    std::vector<void *> wf_allocs;
+    unsigned long long *h_pinned = nullptr;
+    bool pending_wavefront = false; uint64_t pending_paths = 0;
 };
 
 namespace {
@@ -192,6 +199,27 @@ int ensure_image_buffers(rtow_scene *s, size_t pixels) {
     return RTOW_OK;
 }
 
+int ensure_wavefront(rtow_scene *s, int pool, size_t pixels) {
+    if (pool <= s->wf_pool && pixels <= s->wf_pixels) return RTOW_OK;
+    for (void *p : s->wf_allocs) cudaFree(p);
+    s->wf_allocs.clear(); s->wf_pool = 0; s->wf_pixels = 0;
+    pool = std::max(pool, s->wf_pool); pixels = std::max(pixels, s->wf_pixels);
+    auto grab = [&](void **p, size_t bytes) { cudaError_t e = cudaMalloc(p, bytes); if (e == cudaSuccess) s->wf_allocs.push_back(*p); return e; };
+    WavefrontLaunch &W = s->wf;
+    CUDA_TRY(grab((void **)&W.rayA, (size_t)pool * 16)); CUDA_TRY(grab((void **)&W.rayB, (size_t)pool * 16));
+    CUDA_TRY(grab((void **)&W.hit, (size_t)pool * 8));
+    CUDA_TRY(grab((void **)&W.thr, (size_t)pool * 16)); CUDA_TRY(grab((void **)&W.rad, (size_t)pool * 16));
+    CUDA_TRY(grab((void **)&W.ids, (size_t)pool * 16));
+    CUDA_TRY(grab((void **)&W.queue, (size_t)pool * RTOW_WF_MAX_CLASSES * 4));
+    CUDA_TRY(grab((void **)&W.counts, 2 * RTOW_WF_MAX_CLASSES * 4));
+    CUDA_TRY(grab((void **)&W.fixed, pixels * 3 * 8));
+    CUDA_TRY(grab((void **)&W.control, RTOW_WF_CONTROL_WORDS * 8));
+    W.next_item = W.control; W.dead_slots = W.control + 1; W.extend_head = W.control + 2; W.stats = W.control + 3;
+    if (!s->h_pinned) CUDA_TRY(cudaMallocHost((void **)&s->h_pinned, 64));
+    s->wf_pool = pool; s->wf_pixels = pixels;
+    return RTOW_OK;
+}
+
 int resolve_traverse(const rtow_scene *s, int traverse, int *out) {
     if (traverse == RTOW_TRAVERSE_AUTO) traverse = s->has_fast ? RTOW_TRAVERSE_FAST : RTOW_TRAVERSE_EXACT;
     if (traverse != RTOW_TRAVERSE_EXACT && traverse != RTOW_TRAVERSE_FAST) return set_error(RTOW_ERR_INVALID_ARG, "unknown traverse mode");
@@ -209,7 +237,6 @@ int check_render_args(const rtow_scene *s, const rtow_camera *cam, const rtow_re
     if (p->max_depth < 0) return set_error(RTOW_ERR_INVALID_ARG, "render: negative max_depth");
     if (p->kernel != RTOW_KERNEL_AUTO && p->kernel != RTOW_KERNEL_MEGA && p->kernel != RTOW_KERNEL_WAVEFRONT)
         return set_error(RTOW_ERR_INVALID_ARG, "render: unknown kernel");
-    if (p->kernel == RTOW_KERNEL_WAVEFRONT) return set_error(RTOW_ERR_UNSUPPORTED, "render: wavefront kernels are not built in this version");
     int trav;
     if (int rc = resolve_traverse(s, p->traverse, &trav)) return rc;
     L->width = p->width; L->height = p->height;
@@ -235,7 +262,7 @@ int rtow_device_count(void) {
 }
 
 const char *rtow_build_info(void) {
-    return "rtow_b200 abi " "1" " | nvcc " __DATE__ " | sm_100a | -fmad=false | kernels: trace, render_mega, resolve";
+    return "rtow_b200 abi " "1" " | nvcc " __DATE__ " | sm_100a | -fmad=false | kernels: trace_persistent, trace, render_mega, wavefront (extend/shade), resolve";
 }
 
 void rtow_scene_destroy(rtow_scene *s) {
@@ -244,6 +271,8 @@ void rtow_scene_destroy(rtow_scene *s) {
     for (void *p : s->allocs) cudaFree(p);
     for (void *p : {(void *)s->d_counters, s->d_rays, s->d_hits, (void *)s->d_accum, (void *)s->d_rgb, (void *)s->d_bgra})
         if (p) cudaFree(p);
+    for (void *p : s->wf_allocs) cudaFree(p);
+    if (s->h_pinned) cudaFreeHost(s->h_pinned);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->stream) cudaStreamDestroy(s->stream);
@@ -285,13 +314,19 @@ int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out)
     }
     if ((rc = upload(s, objs.data(), objs.size(), &D.objects))) return rc;
 
+    // shading class of a material = (material type, root texture type), numbered densely from 1 (0 = miss); the
+    // wavefront path queues slots by class so that a warp shades one kind of surface
+    std::vector<int> class_of_key(64, -1);
+    int n_classes = 1;
     std::vector<int4> mats((size_t)desc->n_materials * 2);
     for (int i = 0; i < desc->n_materials; ++i) {
         const rtow_material &m = desc->materials[i];
         int32_t f[4]; std::memcpy(f, m.f, 16);
         bool textured = m.type == RTOW_MAT_LAMBERTIAN || m.type == RTOW_MAT_DIFFUSE_LIGHT || m.type == RTOW_MAT_ISOTROPIC;
         mats[2 * i] = make_int4(m.type, m.tex_id, f[0], f[1]);
-        mats[2 * i + 1] = make_int4(f[2], f[3], textured && texture_needs_uv(desc, m.tex_id) ? 1 : 0, 0);
+        int key = m.type * 8 + (textured ? desc->textures[m.tex_id].type : 7);
+        if (class_of_key[key] < 0) class_of_key[key] = n_classes < RTOW_WF_MAX_CLASSES ? n_classes++ : RTOW_WF_MAX_CLASSES - 1;
+        mats[2 * i + 1] = make_int4(f[2], f[3], textured && texture_needs_uv(desc, m.tex_id) ? 1 : 0, class_of_key[key]);
     }
     if ((rc = upload(s, mats.data(), mats.size(), &D.materials))) return rc;
 
@@ -435,11 +470,31 @@ int rtow_render_accumulate_device(rtow_scene *s, const rtow_camera *cam, const r
     cudaStream_t st = (cudaStream_t)stream;
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTOW_N_COUNTERS * sizeof(unsigned long long), st));
     CUDA_TRY(cudaEventRecord(s->ev0, st));
-    launch_render_mega(s->d, *cam, L, d_accum, s->d_counters, false, st);
+    static const int auto_kernel = [] { const char *e = getenv("RTOW_KERNEL"); return e ? atoi(e) : RTOW_KERNEL_MEGA; }();
+    const int kernel = params->kernel == RTOW_KERNEL_AUTO ? auto_kernel : params->kernel;
+    if (kernel == RTOW_KERNEL_WAVEFRONT) {
+        // Synchronises `stream` internally (the host loop polls the pool for completion).
+        static const long long pool_cap = [] { const char *e = getenv("RTOW_WF_POOL"); return e ? atoll(e) : (1ll << 20); }();
+        const long long n_pixels = (long long)L.width * L.height;
+        const unsigned long long items = (unsigned long long)((n_pixels + 31) / 32) * 32ull * (unsigned)L.sample_count;
+        long long pool = (long long)std::min<unsigned long long>(items, (unsigned long long)pool_cap);
+        pool = (pool + 255) / 256 * 256;
+        if (int rc = ensure_wavefront(s, (int)pool, (size_t)n_pixels)) return rc;
+        s->wf.L = L; s->wf.pool = (int)pool; s->wf.total_items = items;
+        uint32_t launches = 0;
+        CUDA_TRY(run_wavefront(s->d, *cam, s->wf, d_accum, s->h_pinned, st, &launches));
+        CUDA_TRY(cudaMemcpyAsync(s->d_counters, s->wf.stats, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st));
+        s->pending_launches = launches;
+        s->pending_wavefront = true;
+        s->pending_paths = (uint64_t)n_pixels * (uint64_t)L.sample_count;
+    } else {
+        launch_render_mega(s->d, *cam, L, d_accum, s->d_counters, false, st);
+        s->pending_launches = 1;
+        s->pending_wavefront = false;
+    }
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaEventRecord(s->ev1, st));
     s->pending = true;
-    s->pending_launches = 1;
     return RTOW_OK;
 }
 
@@ -476,7 +531,7 @@ int rtow_stream_stats(rtow_scene *s, void *stream, rtow_stats *stats) {
     if (!s->pending) return RTOW_OK;
     unsigned long long c[RTOW_N_COUNTERS];
     CUDA_TRY(cudaMemcpy(c, s->d_counters, sizeof c, cudaMemcpyDeviceToHost));
-    stats->rays = c[0]; stats->paths = c[1];
+    stats->rays = c[0]; stats->paths = s->pending_wavefront ? s->pending_paths : c[1];
     CUDA_TRY(cudaEventElapsedTime(&stats->kernel_ms, s->ev0, s->ev1));
     stats->total_ms = stats->kernel_ms;
     stats->launches = s->pending_launches;

@@ -24,6 +24,29 @@ void launch_trace(const DScene &S, const rtow_ray *d_rays, uint64_t n, rtow_hit 
                   unsigned long long *d_counters, bool count, cudaStream_t stream);
 void launch_render_mega(const DScene &S, const rtow_camera &cam, const RenderLaunch &L, float *d_accum,
                         unsigned long long *d_counters, bool count, cudaStream_t stream);
+// ---- wavefront path (wavefront.cu) --------------------------------------------------------------------------
+enum { RTOW_WF_MAX_CLASSES = 16, RTOW_WF_CONTROL_WORDS = 8 };
+#ifndef RTOW_WF_STACK_SMEM
+#define RTOW_WF_STACK_SMEM 12
+#endif
+struct WavefrontLaunch {
+    RenderLaunch L;
+    int pool;                             // path slots (multiple of 256)
+    unsigned long long total_items;       // work items = pixel groups of 32 x samples (incl. padding pixels)
+    // per-slot state (SoA in HBM)
+    float4 *rayA, *rayB;                  // {o.xyz, time} {d.xyz, -}
+    float2 *hit;                          // {t, prim id bits} (prim < 0: miss)
+    float4 *thr, *rad;                    // path throughput T, radiance so far L
+    int4 *ids;                            // {pixel, sample, next Philox draw, depth}; depth < 0: the slot is dead
+    int *queue;                           // RTOW_WF_MAX_CLASSES x pool slot indices, by shading class
+    unsigned *counts;                     // 2 x RTOW_WF_MAX_CLASSES queue lengths (double-buffered by bounce parity)
+    unsigned long long *fixed;            // W*H*3 radiance sums, Q31.32
+    unsigned long long *control;          // [0] next work item [1] dead slots [2] extend queue head [3] rays traced
+    unsigned long long *next_item, *dead_slots, *extend_head, *stats;
+};
+cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaunch &W, float *d_accum, unsigned long long *h_pinned,
+                          cudaStream_t stream, uint32_t *launches_out);
+
 void launch_resolve(const float *d_accum, int width, int height, int spp, float *d_rgb, uint8_t *d_bgra, cudaStream_t stream);
 
 }  // namespace rtow

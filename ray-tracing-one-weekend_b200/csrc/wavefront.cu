@@ -1,0 +1,336 @@
+// wavefront.cu -- RTOW_KERNEL_WAVEFRONT: the pixel/sample loop + color() (main.cpp:932-956, color.h:12-59) as a pool
+// of path states in HBM advanced by two kernels per bounce:
+//
+//   wf_extend_kernel   world->hit() for every live slot: the persistent, vote-scheduled closest-hit traversal of
+//                      kernels.cu (lanes refill from a global counter), writes {t, prim} and appends the slot to the
+//                      queue of its shading class (miss / material x root texture) with warp-aggregated atomics
+//   wf_shade_kernel    one thread per queued slot, queues laid out class after class so that a warp shades one class:
+//                      emitted + scatter (material.h), textures / Perlin (texture.h, noise.h), sky on a miss; a path
+//                      that ends adds its radiance to the pixel (64-bit fixed point: order-independent, so the image
+//                      is deterministic although slots are handed out dynamically) and the slot starts the next
+//                      (pixel, sample) work item from a global counter (camera.h:123-135) -- no separate generate pass
+//                      after the first
+//   wf_finalize_kernel fixed-point sums -> += the caller's fp32 accumulators
+//
+// Path arithmetic is the megakernel's, instruction for instruction (same headers), and the Philox stream of a path is
+// keyed by (pixel, sample) only: both kernels render the same image up to the order of the per-pixel sum.
+// Built with -fmad=false like kernels.cu.
+#include "rt_kernels.cuh"
+#include "rt_shade.cuh"
+#include "rt_fast.cuh"
+
+#include <algorithm>
+#include <cstdlib>
+
+namespace rtow {
+
+#define WF_FIXED_SCALE 4294967296.0   // 2^32: radiance sums in Q31.32
+
+__device__ __forceinline__ void wf_item_to_pixel(const WavefrontLaunch &W, unsigned long long item, int &pixel, int &sample) {
+    // 32 neighbouring pixels x all samples form a group; inside it consecutive items are consecutive pixels of ONE
+    // sample index, so the 32 lanes of a warp start coherent primary rays and add to 32 different pixels
+    const unsigned long long per_group = 32ull * (unsigned)W.L.sample_count;
+    const unsigned long long g = item / per_group, j = item % per_group;
+    pixel = (int)(g * 32ull + (j & 31ull));
+    sample = (int)(j >> 5);
+}
+
+// Starts the path of work item `item` in `slot` (main.cpp:943-948).  Returns false for the padding pixels of the last group.
+__device__ __forceinline__ bool wf_start_path(const WavefrontLaunch &W, const rtow_camera &cam, unsigned long long item, int slot) {
+    int pixel, s;
+    wf_item_to_pixel(W, item, pixel, s);
+    if (pixel >= W.L.width * W.L.height) return false;
+    const int x = pixel % W.L.width, y = pixel / W.L.width;
+    const int row = W.L.height - 1 - y;
+    Rng g;
+    rng_init(g, W.L.seed, (uint32_t)pixel, (uint32_t)(W.L.sample_begin + s));
+    float ju = rng_next(g), jv = rng_next(g);
+    float u = (float)((double)x + (double)ju) / (float)W.L.width;
+    float v = (float)((double)row + (double)jv) / (float)W.L.height;
+    Ray r;
+    camera_ray(cam, u, v, g, r);
+    W.rayA[slot] = make_float4(r.ox, r.oy, r.oz, r.time);
+    W.rayB[slot] = make_float4(r.dx, r.dy, r.dz, 0.f);
+    W.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+    W.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+    W.ids[slot] = make_int4(pixel, W.L.sample_begin + s, (int)g.next, 0);
+    return true;
+}
+
+// Hands the next work items to the lanes with need == true (all 32 lanes must call).  A lane whose items run out
+// gets dead = true.  Padding items are skipped by asking again.
+__device__ __forceinline__ void wf_refill(const WavefrontLaunch &W, const rtow_camera &cam, bool need, int slot, bool &dead) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    dead = false;
+    for (;;) {
+        const unsigned m = __ballot_sync(full, need);
+        if (m == 0) break;
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(W.next_item, (unsigned long long)__popc(m));
+        base = __shfl_sync(full, base, 0);
+        if (need) {
+            const unsigned long long item = base + __popc(m & ((1u << lane) - 1u));
+            if (item >= W.total_items) { dead = true; need = false; }
+            else if (wf_start_path(W, cam, item, slot)) need = false;
+        }
+    }
+    const unsigned dm = __ballot_sync(full, dead);
+    if (dead) W.ids[slot].w = -1;
+    if (lane == 0 && dm) atomicAdd(W.dead_slots, (unsigned long long)__popc(dm));
+}
+
+__global__ void __launch_bounds__(256) wf_generate_kernel(WavefrontLaunch W, rtow_camera cam) {
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;     // the grid covers the pool exactly (pool % 256 == 0)
+    bool dead;
+    wf_refill(W, cam, true, slot, dead);
+}
+
+// ---- extend ------------------------------------------------------------------------------------------------
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, WavefrontLaunch W, int parity, int refill_below, int leaf_min) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    __shared__ int s_ref[RTOW_WF_STACK_SMEM * 128];
+    __shared__ float s_d[RTOW_WF_STACK_SMEM * 128];
+    SmemStack<RTOW_WF_STACK_SMEM> st;
+    st.sref = s_ref + (threadIdx.x >> 5) * (RTOW_WF_STACK_SMEM * 32) + lane;
+    st.sd = s_d + (threadIdx.x >> 5) * (RTOW_WF_STACK_SMEM * 32) + lane;
+    FastTrav T;
+    T.cur = RTOW_TRAV_DONE; T.sp = 0;
+    int slot = 0;
+    bool has_ray = false, more = true;
+    unsigned long long rays = 0;
+    RngKey key;
+    key.seed = W.L.seed; key.pixel = key.sample = key.bounce = 0;
+    unsigned *counts = W.counts + parity * RTOW_WF_MAX_CLASSES;
+    const bool use_fast = W.L.traverse == RTOW_TRAVERSE_FAST && S.fast_nodes != nullptr;
+
+    for (;;) {
+        // 1. finished lanes: write {t, prim} and queue the slot under its shading class
+        {
+            const bool fin = has_ray && T.cur == RTOW_TRAV_DONE;
+            if (__any_sync(full, fin)) {
+                int cls = -1;
+                if (fin) {
+                    float t = 0.f; int pid = -1;
+                    if (!fast_result(S, T, t, pid)) pid = -1;
+                    W.hit[slot] = make_float2(t, __int_as_float(pid));
+                    cls = pid >= 0 ? __ldg(&S.materials[2 * __ldg(&S.prims[pid * 5]).y + 1]).w : 0;
+                    has_ray = false;
+                }
+                const unsigned same = __match_any_sync(full, cls);
+                if (cls >= 0) {
+                    const int leader = __ffs(same) - 1;
+                    unsigned base = 0;
+                    if (lane == leader) base = atomicAdd(&counts[cls], (unsigned)__popc(same));
+                    base = __shfl_sync(same, base, leader);
+                    W.queue[(size_t)cls * W.pool + base + __popc(same & ((1u << lane) - 1u))] = slot;
+                }
+            }
+        }
+        // 2. idle lanes take the next slots of the pool; dead slots are skipped
+        if (more) {
+            const unsigned need = __ballot_sync(full, !has_ray);
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(W.extend_head, (unsigned long long)__popc(need));
+            base = __shfl_sync(full, base, 0);
+            if (base + __popc(need) >= (unsigned long long)W.pool) more = false;
+            if (!has_ray) {
+                const unsigned long long mine = base + __popc(need & ((1u << lane) - 1u));
+                if (mine < (unsigned long long)W.pool) {
+                    const int4 id = W.ids[mine];
+                    if (id.w >= 0) {
+                        slot = (int)mine; has_ray = true; rays++;
+                        const float4 a = W.rayA[slot], b = W.rayB[slot];
+                        Ray r;
+                        r.ox = a.x; r.oy = a.y; r.oz = a.z; r.time = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z;
+                        key.pixel = (uint32_t)id.x; key.sample = (uint32_t)id.y; key.bounce = (uint32_t)id.w;
+                        chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, r);
+                        if (use_fast && fast_covers(S, r, 0.001f, FLT_MAX)) {
+                            fast_begin(S, r, 0.001f, FLT_MAX, T);
+                        } else {
+                            // list scenes (nothing to cull) and rays outside the culling argument: the reference walk
+                            Rng g;
+                            rng_init(g, key.seed, key.pixel, key.sample);
+                            g.bounce = key.bounce;
+                            float t; int pid; unsigned nv = 0, pt = 0;
+                            T.best_obj = -1; T.best_prim = -1;
+                            if (closest_hit_exact<false>(S, r, 0.001f, FLT_MAX, &g, t, pid, nv, pt)) { T.best = t; T.best_obj = 0; T.best_prim = pid; }
+                            T.cur = RTOW_TRAV_DONE;
+                        }
+                    }
+                }
+            }
+        }
+        if (!__any_sync(full, has_ray)) { if (!more) break; else continue; }
+        // 3. vote-scheduled traversal rounds (see trace_persistent_kernel)
+        for (;;) {
+            fast_pop_one(T, st);
+            const bool at_node = fast_at_node(T), at_leaf = fast_at_leaf(T);
+            const unsigned mn = __ballot_sync(full, at_node), ml = __ballot_sync(full, at_leaf);
+            const unsigned alive = __ballot_sync(full, T.cur != RTOW_TRAV_DONE);
+            if (alive == 0 || (more && __popc(alive) < refill_below)) break;
+            unsigned nv = 0, pt = 0;
+            if (ml == 0 || (mn != 0 && __popc(ml) < leaf_min)) {
+                if (at_node) fast_node<false>(S, T, st, nv);
+            } else {
+                if (at_leaf) fast_leaf<false>(S, T, key, pt);
+            }
+        }
+    }
+    for (int off = 16; off; off >>= 1) rays += __shfl_down_sync(full, rays, off);
+    if (lane == 0 && rays) atomicAdd(&W.stats[0], rays);
+}
+
+// ---- shade -------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void wf_add_pixel(const WavefrontLaunch &W, int pixel, const float L[3]) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float v = L[k];
+        if (v != 0.f && fabsf(v) <= 1e9f)      // NaN / inf / absurd radiance never reaches the sum (reference: undefined, main.cpp:963)
+            atomicAdd(&W.fixed[(size_t)pixel * 3 + k], (unsigned long long)__double2ll_rn((double)v * WF_FIXED_SCALE));
+    }
+}
+
+__global__ void __launch_bounds__(256) wf_shade_kernel(DScene S, WavefrontLaunch W, rtow_camera cam, int parity) {
+    __shared__ PerlinSmem perlin;
+    perlin_stage(S, &perlin);
+    __syncthreads();
+
+    const unsigned *counts = W.counts + parity * RTOW_WF_MAX_CLASSES;
+    const unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j == 0) {
+        // the extend launch of this bounce is complete: reset what the next one uses
+        *W.extend_head = 0ull;
+        unsigned *other = W.counts + (parity ^ 1) * RTOW_WF_MAX_CLASSES;
+        for (int c = 0; c < RTOW_WF_MAX_CLASSES; ++c) other[c] = 0u;
+    }
+    // queues are consumed class after class: thread j -> (class, index)
+    int slot = -1;
+    {
+        unsigned off = 0;
+        for (int c = 0; c < RTOW_WF_MAX_CLASSES; ++c) {
+            const unsigned n = counts[c];
+            if (j >= off && j < off + n) { slot = W.queue[(size_t)c * W.pool + (j - off)]; break; }
+            off += n;
+        }
+    }
+    const bool valid = slot >= 0;
+    bool ended = false;
+    int pixel = 0;
+    float Lr[3] = {0.f, 0.f, 0.f};
+    if (valid) {
+        const int4 id = W.ids[slot];
+        const float4 a = W.rayA[slot], b = W.rayB[slot];
+        const float2 hr = W.hit[slot];
+        const float4 t4 = W.thr[slot], l4 = W.rad[slot];
+        float T[3] = {t4.x, t4.y, t4.z};
+        Lr[0] = l4.x; Lr[1] = l4.y; Lr[2] = l4.z;
+        pixel = id.x;
+        int depth = id.w;
+        Ray r;
+        r.ox = a.x; r.oy = a.y; r.oz = a.z; r.time = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z;
+        Rng g;
+        rng_init(g, W.L.seed, (uint32_t)id.x, (uint32_t)id.y);
+        g.next = (uint32_t)id.z; g.bounce = (uint32_t)depth;
+        const int pid = __float_as_int(hr.y);
+        // ---- color.h:12-59, iterative: L += T*E ; T *= A (the megakernel's body) ----
+        if (pid < 0) {
+            if (W.L.global_illum_en) {
+                if (depth < 1) {                                              // color.h:35-50
+                    float ux, uy, uz;
+                    unit3(r.dx, r.dy, r.dz, ux, uy, uz);
+                    float k = (float)(1.0 + (double)uz);
+                    float sky0 = (float)((double)k * 0.1), sky1 = (float)((double)k * 0.3), sky2 = (float)((double)k * 1.0);
+                    Lr[0] += T[0] * (W.L.sky_gain * sky0); Lr[1] += T[1] * (W.L.sky_gain * sky1); Lr[2] += T[2] * (W.L.sky_gain * sky2);
+                } else {                                                      // color.h:52-54
+                    Lr[0] += T[0] * W.L.ambient_gain; Lr[1] += T[1] * W.L.ambient_gain; Lr[2] += T[2] * W.L.ambient_gain;
+                }
+            }
+            ended = true;
+        } else {
+            Ray rl = r;
+            chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, rl);
+            MatRec m = load_material(S, __ldg(&S.prims[pid * 5]).y);
+            Hit h;
+            prim_record(S, pid, rl, hr.x, m.needs_uv != 0, h);
+            float em[3];
+            if (depth < W.L.max_depth) {
+                float atten[3], sd[3], stime;
+                float rd[3] = {r.dx, r.dy, r.dz};
+                bool go = scatter(S, &perlin, m, h, rd, r.time, g, atten, sd, stime, em);
+                Lr[0] += T[0] * em[0]; Lr[1] += T[1] * em[1]; Lr[2] += T[2] * em[2];
+                if (go) {
+                    T[0] *= atten[0]; T[1] *= atten[1]; T[2] *= atten[2];
+                    W.rayA[slot] = make_float4(h.p[0], h.p[1], h.p[2], stime);
+                    W.rayB[slot] = make_float4(sd[0], sd[1], sd[2], 0.f);
+                    W.thr[slot] = make_float4(T[0], T[1], T[2], 0.f);
+                    W.rad[slot] = make_float4(Lr[0], Lr[1], Lr[2], 0.f);
+                    W.ids[slot] = make_int4(id.x, id.y, (int)g.next, depth + 1);
+                } else {
+                    ended = true;
+                }
+            } else {
+                if (m.type == RTOW_MAT_DIFFUSE_LIGHT) {                        // color.h:25-30
+                    texture_value(S, &perlin, m.tex, h.u, h.v, h.p, em);
+                    Lr[0] += T[0] * em[0]; Lr[1] += T[1] * em[1]; Lr[2] += T[2] * em[2];
+                }
+                ended = true;
+            }
+        }
+    }
+    if (ended) wf_add_pixel(W, pixel, Lr);
+    bool dead;
+    wf_refill(W, cam, ended, valid ? slot : 0, dead);
+}
+
+__global__ void wf_finalize_kernel(const unsigned long long *__restrict__ fixed, float *__restrict__ accum, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const long long q = (long long)fixed[i];
+    accum[i] += (float)((double)q * (1.0 / WF_FIXED_SCALE));
+}
+
+// ---- host driver ---------------------------------------------------------------------------------------------
+cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaunch &W, float *d_accum, unsigned long long *h_pinned,
+                          cudaStream_t stream, uint32_t *launches_out) {
+    static const int refill = [] { const char *e = getenv("RTOW_TRACE_REFILL"); return e ? atoi(e) : 24; }();
+    static const int leaf_min = [] { const char *e = getenv("RTOW_TRACE_LEAFMIN"); return e ? atoi(e) : 8; }();
+    int dev = 0, sms = 148, per_sm = 4;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_extend_kernel<5>, 128, 0);
+    const unsigned ext_blocks = (unsigned)std::min<long long>((W.pool + 127) / 128, (long long)sms * std::max(per_sm, 1));
+    const unsigned pool_blocks = (unsigned)(W.pool / 256);
+    const size_t n_acc = (size_t)W.L.width * W.L.height * 3;
+    uint32_t launches = 0;
+
+    cudaMemsetAsync(W.fixed, 0, n_acc * sizeof(unsigned long long), stream);
+    cudaMemsetAsync(W.control, 0, RTOW_WF_CONTROL_WORDS * sizeof(unsigned long long), stream);
+    cudaMemsetAsync(W.counts, 0, 2 * RTOW_WF_MAX_CLASSES * sizeof(unsigned), stream);
+    wf_generate_kernel<<<pool_blocks, 256, 0, stream>>>(W, cam);
+    launches++;
+    // Every slot traces one ray per iteration; slots die only when the work items run out, so the loop needs about
+    // total_rays / pool iterations plus a tail of at most max_depth.  The dead-slot counter is read back every few
+    // iterations (the reads lag the launches; extra iterations over a dead pool cost ~10 us each).
+    int parity = 0;
+    for (long long it = 0;; ++it) {
+        wf_extend_kernel<5><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min);
+        wf_shade_kernel<<<pool_blocks, 256, 0, stream>>>(S, W, cam, parity);
+        launches += 2;
+        parity ^= 1;
+        if ((it & 7) == 7 || W.total_items <= (unsigned long long)W.pool) {
+            cudaMemcpyAsync(h_pinned, W.dead_slots, sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream);
+            cudaError_t e = cudaStreamSynchronize(stream);
+            if (e != cudaSuccess) return e;
+            if (*h_pinned >= (unsigned long long)W.pool) break;
+        }
+    }
+    wf_finalize_kernel<<<(unsigned)((n_acc + 255) / 256), 256, 0, stream>>>(W.fixed, d_accum, n_acc);
+    launches++;
+    if (launches_out) *launches_out = launches;
+    return cudaGetLastError();
+}
+
+}  // namespace rtow

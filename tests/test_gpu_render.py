@@ -23,9 +23,11 @@ def _render_pair(gpu, abi, port, name, kw, W, H, spp, seed=7, **pk):
 
 
 @pytest.mark.parametrize("name,kw", SCENES)
-def test_render_matches_oracle(gpu, abi, port, name, kw):
+@pytest.mark.parametrize("kernel", ["mega", "wavefront"])
+def test_render_matches_oracle(gpu, abi, port, name, kw, kernel):
     W, H, spp = 96, 54, 8
-    img, st, want, _ = _render_pair(gpu, abi, port, name, kw, W, H, spp)
+    img, st, want, _ = _render_pair(gpu, abi, port, name, kw, W, H, spp,
+                                    kernel=abi.KERNEL_MEGA if kernel == "mega" else abi.KERNEL_WAVEFRONT)
     ref = want["sum"] / np.float32(spp)
     assert st.paths == W * H * spp
     assert st.rays == want["rays"], "ray count differs: the GPU traced different paths than the oracle"
@@ -36,17 +38,36 @@ def test_render_matches_oracle(gpu, abi, port, name, kw):
     assert rmse <= 1e-3, f"{name}: RMSE {rmse}"
 
 
-def test_depth_limit_and_no_global_illum(gpu, abi, port):
+@pytest.mark.parametrize("kernel", [1, 2])
+def test_depth_limit_and_no_global_illum(gpu, abi, port, kernel):
     for depth, gi in ((0, 1), (1, 1), (3, 0)):
         host = gpu.HostScene("cornell_smoke_ned", seed=1)
         dev = gpu.DeviceScene(host.desc)
         cam = gpu.main_camera(64, 36)
-        params = abi.default_render_params(64, 36, 4, seed=5, max_depth=depth)
+        params = abi.default_render_params(64, 36, 4, seed=5, max_depth=depth, kernel=kernel)
         params.global_illum_en = gi
         img, st = dev.render(cam, params)
         want = port.render(host.desc, cam, params)
         assert st.rays == want["rays"]
         assert np.abs(img - want["sum"] / np.float32(4)).max() <= 2e-4 * max(1.0, float(want["sum"].max()) / 4)
+
+
+def test_wavefront_equals_megakernel(gpu, abi):
+    """Same Philox streams, same path arithmetic: the two kernels differ only in the order of the per-pixel sum
+    (fp32 shuffles vs 64-bit fixed point), and the wavefront image is deterministic although slots are handed out
+    dynamically.  A pool smaller than the work (forced regeneration) must not change the image."""
+    import os
+    host = gpu.HostScene("random_ned", seed=12345, image=earth_image())
+    dev = gpu.DeviceScene(host.desc)
+    W, H, spp = 160, 90, 32
+    cam = gpu.main_camera(W, H)
+    a, sa = dev.render(cam, abi.default_render_params(W, H, spp, seed=4, kernel=abi.KERNEL_MEGA))
+    b, sb = dev.render(cam, abi.default_render_params(W, H, spp, seed=4, kernel=abi.KERNEL_WAVEFRONT))
+    c, sc = dev.render(cam, abi.default_render_params(W, H, spp, seed=4, kernel=abi.KERNEL_WAVEFRONT))
+    assert sa.rays == sb.rays == sc.rays and sa.paths == sb.paths == W * H * spp
+    assert b.tobytes() == c.tobytes()
+    assert np.allclose(a, b, rtol=2e-5, atol=2e-6)
+    assert sb.launches > 3
 
 
 def test_render_is_deterministic_and_shard_invariant(gpu, abi):
