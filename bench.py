@@ -37,7 +37,7 @@ WORKLOAD = "configs[1]: random-spheres scene (randomScene_NED + main.cpp camera)
 
 # Algorithmic work per unit, in fp32 lane-operations (DESIGN.md "Work model").
 OPS_SLAB = 27          # ray-AABB slab test, division form (aabb.h:22-43)
-OPS_NODE4 = 4 * 14 + 20  # fast traversal: 4 child boxes (6 fma + 6 min/max + 2) + ordering network
+OPS_NODE4 = 4 * 28 + 25  # fast traversal: 4 child boxes (6 plane fma + 5 exit bound + 3 slack + 12 inflated near/far + 2) + ordering network
 OPS_PRIM = 24          # ray-sphere test, miss path (sphere.h:26-42); rect = 12
 OPS_HIT = 42           # accepted hit: root, point, normal
 OPS_SCATTER = 32       # Lambertian scatter incl. E[1.91] rejection rounds
@@ -285,10 +285,25 @@ def run_product(args):
     rays_per_path = wc.rays / max(1, wc.paths)
     my_paths = float(W) * H * n
     my_rays = float(st.rays)
-    ops_launch = my_rays * ops_per_ray + my_paths * OPS_PATH
     sms, mhz = sm_count_and_clock(torch)
     peak_tops = sms * 128 * mhz * 1e6 / 1e12
-    achieved_tops = ops_launch / (kern_ms_last * 1e-3) / 1e12
+    prof = scene.render_profile()
+    step_tops = (my_rays * ops_per_ray + my_paths * OPS_PATH) / (kern_ms_last * 1e-3) / 1e12
+    if prof.kernel == abi.KERNEL_WAVEFRONT and prof.sampled_iterations > 0:
+        # dominant kernel = wf_extend_kernel (world->hit for one bounce of the whole pool): traversal work only
+        ext_ms = prof.extend_ms_sum / prof.sampled_iterations
+        shade_ms = prof.shade_ms_sum / prof.sampled_iterations
+        trav_ops_per_ray = box_ops * wc.node_visits_per_ray + OPS_PRIM * wc.prim_tests_per_ray
+        achieved_tops = prof.pool_slots * trav_ops_per_ray / (ext_ms * 1e-3) / 1e12
+        dom = {"kernel": "wf_extend_kernel", "kernel_ms": ext_ms, "launches_per_step": prof.iterations, "units_per_launch": prof.pool_slots,
+               "ops_per_unit": trav_ops_per_ray, "share_of_step": ext_ms / (ext_ms + shade_ms), "shade_kernel_ms": shade_ms,
+               "sampled_launches": prof.sampled_iterations}
+        kernel_name = "wavefront"
+    else:
+        achieved_tops = step_tops
+        dom = {"kernel": "render_mega_kernel", "kernel_ms": kern_ms_last, "launches_per_step": 1, "units_per_launch": my_rays,
+               "ops_per_unit": ops_per_ray, "share_of_step": 1.0}
+        kernel_name = "megakernel"
     # HBM view: algorithmic bytes = accumulator read+write once per launch (+ the scene, KBs)
     alg_bytes = W * H * 3 * 4 * 2
     try:
@@ -310,13 +325,13 @@ def run_product(args):
         p, r, s = stepf()
         cpu = {"value": p / s / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": kind, "sample": sample, "mrays_per_s": r / s / 1e6}
 
-    launches_per_step = 1 + 1   # render_mega_kernel + resolve_kernel (rank 0); NCCL's kernels are not ours
+    launches_per_step = int(st.launches) + 1   # this rank's render kernels + resolve_kernel (rank 0); NCCL's kernels are not ours
     line = {
         "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD if (W, H, spp) == (WIDTH, HEIGHT, SPP) else f"random-spheres scene {W}x{H}, {spp} spp, depth {DEPTH}",
                    "scene_seed": SCENE_SEED, "render_seed": RENDER_SEED, "parallelism": f"spp-sharded x{world}, NCCL sum-reduce of fp32 accumulators",
-                   "kernel": "megakernel", "traverse": {1: "exact", 2: "fast"}[wc.traverse],
+                   "kernel": kernel_name, "traverse": {1: "exact", 2: "fast"}[wc.traverse],
                    "l2": "flushed between timed iterations (256 MiB fill); scene is L2-resident by design"},
         "mrays_per_s": rays_per_step / (ms_step * 1e-3) / 1e6,
         "rays_per_path": rays_per_path,
@@ -324,11 +339,11 @@ def run_product(args):
                 "d2h_bytes_per_step": W * H * 3 * 4 + W * H * 4, "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,
-        "roofline": {"bound": "fp32_issue", "achieved": achieved_tops, "peak": peak_tops, "unit": "Tlaneop/s", "frac": achieved_tops / peak_tops,
-                     "traffic": None, "kernel": "render_mega_kernel", "kernel_ms": kern_ms_last,
-                     "peak_source": f"{sms} SMs x 128 fp32 lanes x {mhz:.0f} MHz (clocks.max.sm)",
-                     "ops_per_ray": ops_per_ray, "node_visits_per_ray": wc.node_visits_per_ray, "prim_tests_per_ray": wc.prim_tests_per_ray,
-                     "noise_evals_per_ray": wc.noise_evals_per_ray},
+        "roofline": dict({"bound": "fp32_issue", "achieved": achieved_tops, "peak": peak_tops, "unit": "Tlaneop/s", "frac": achieved_tops / peak_tops,
+                          "traffic": None, "peak_source": f"{sms} SMs x 128 fp32 lanes x {mhz:.0f} MHz (clocks.max.sm)",
+                          "whole_step_achieved": step_tops, "whole_step_frac": step_tops / peak_tops,
+                          "ops_per_ray_incl_shading": ops_per_ray, "node_visits_per_ray": wc.node_visits_per_ray,
+                          "prim_tests_per_ray": wc.prim_tests_per_ray, "noise_evals_per_ray": wc.noise_evals_per_ray}, **dom),
         "roofline_hbm": {"bound": "hbm", "achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak, "traffic": None,
                          "peak_source": hbm_src, "note": "accumulator read+write only: this kernel is not HBM-bound"},
         "bvh_hit": bvh,

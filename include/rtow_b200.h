@@ -195,7 +195,7 @@ typedef struct rtow_camera {
 } rtow_camera;
 
 /* ---- render parameters (defines.h:3-30 become run-time fields) ------------ */
-enum { RTOW_KERNEL_AUTO = 0, RTOW_KERNEL_MEGA = 1, RTOW_KERNEL_WAVEFRONT = 2 };
+enum { RTOW_KERNEL_AUTO = 0 /* = wavefront: the measured winner on B200 */, RTOW_KERNEL_MEGA = 1, RTOW_KERNEL_WAVEFRONT = 2 };
 enum {
     RTOW_TRAVERSE_AUTO = 0,
     RTOW_TRAVERSE_EXACT = 1,  /* walks the reference tree as is: both children, no distance culling (bvhNode.h:66-96) */
@@ -252,8 +252,9 @@ int rtow_render(rtow_scene *scene, const rtow_camera *cam, const rtow_render_par
                 float *rgb_linear_out, uint8_t *bgra8_out, rtow_stats *stats);
 
 /* Adds the radiance SUM of samples [sample_begin, +sample_count) into d_accum (W*H*3 floats
- * on the scene's device, row 0 = top).  Asynchronous on `stream`; stats (nullable) are valid
- * after the stream is synchronised by rtow_stream_stats. */
+ * on the scene's device, row 0 = top).  All work is issued on `stream`; the megakernel path returns without
+ * waiting, the wavefront path polls the path pool for completion and so synchronises `stream` before returning.
+ * Counters are read with rtow_stream_stats. */
 int rtow_render_accumulate_device(rtow_scene *scene, const rtow_camera *cam,
                                   const rtow_render_params *params, float *d_accum, void *stream);
 /* Blocks until `stream` is idle and returns the counters of the last accumulate call. */
@@ -280,6 +281,17 @@ typedef struct rtow_work_counters {
 } rtow_work_counters;
 int rtow_render_counters(rtow_scene *scene, const rtow_camera *cam, const rtow_render_params *params,
                          rtow_work_counters *out);
+
+/* Per-kernel timing of the last accumulate/render call on this scene (wavefront path): CUDA events around the
+ * extend and shade launches of every 8th bounce iteration that ran on a full pool.  Used by bench.py's roofline. */
+typedef struct rtow_render_profile_t {
+    int32_t kernel;                 /* RTOW_KERNEL_MEGA or RTOW_KERNEL_WAVEFRONT: what actually ran */
+    uint32_t iterations;            /* bounce iterations (extend + shade launch pairs) */
+    uint32_t pool_slots;            /* path slots = rays per full-pool extend launch */
+    uint32_t sampled_iterations;
+    float extend_ms_sum, shade_ms_sum;   /* over the sampled iterations */
+} rtow_render_profile_t;
+int rtow_render_profile(rtow_scene *scene, rtow_render_profile_t *out);
 
 const char *rtow_last_error(void);
 const char *rtow_build_info(void);

@@ -125,6 +125,17 @@ class Stats(C.Structure):
     ]
 
 
+class RenderProfile(C.Structure):
+    _fields_ = [
+        ("kernel", C.c_int32),
+        ("iterations", C.c_uint32),
+        ("pool_slots", C.c_uint32),
+        ("sampled_iterations", C.c_uint32),
+        ("extend_ms_sum", C.c_float),
+        ("shade_ms_sum", C.c_float),
+    ]
+
+
 class WorkCounters(C.Structure):
     _fields_ = [
         ("paths", C.c_uint64),

@@ -51,6 +51,7 @@ def lib():
         "rtow_resolve_device": (C.c_int, [vp, vp, i32, i32, i32, vp, vp, vp]),
         "rtow_trace_counters": (C.c_int, [vp, vp, u64, C.c_int, P(C.c_double), P(C.c_double)]),
         "rtow_render_counters": (C.c_int, [vp, P(abi.Camera), P(abi.RenderParams), P(abi.WorkCounters)]),
+        "rtow_render_profile": (C.c_int, [vp, P(abi.RenderProfile)]),
         "rtow_last_error": (C.c_char_p, []),
         "rtow_build_info": (C.c_char_p, []),
         "rtow_host_scene_build": (C.c_int, [C.c_char_p, u64, C.c_int, C.c_int, P(vp)]),
@@ -70,7 +71,7 @@ def lib():
 
 EXPORTED_SYMBOLS = [
     "rtow_device_count", "rtow_scene_create", "rtow_scene_destroy", "rtow_trace_rays", "rtow_trace_rays_device",
-    "rtow_render", "rtow_render_accumulate_device", "rtow_stream_stats", "rtow_resolve_device", "rtow_trace_counters", "rtow_render_counters",
+    "rtow_render", "rtow_render_accumulate_device", "rtow_stream_stats", "rtow_resolve_device", "rtow_trace_counters", "rtow_render_counters", "rtow_render_profile",
     "rtow_last_error", "rtow_build_info", "rtow_host_scene_build", "rtow_host_scene_desc", "rtow_host_scene_free",
     "rtow_host_set_image", "rtow_host_camera", "rtow_write_ppm", "rtow_write_pfm",
 ]
@@ -193,6 +194,11 @@ class DeviceScene:
     def render_counters(self, cam, params):
         out = abi.WorkCounters()
         _check(lib().rtow_render_counters(self._h, C.byref(cam), C.byref(params), C.byref(out)))
+        return out
+
+    def render_profile(self):
+        out = abi.RenderProfile()
+        _check(lib().rtow_render_profile(self._h, C.byref(out)))
         return out
 
     def accumulate_device(self, cam, params, d_accum_ptr, stream=None):

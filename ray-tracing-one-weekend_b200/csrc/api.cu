@@ -35,6 +35,7 @@ struct rtow_scene {
     std::vector<void *> wf_allocs;
     unsigned long long *h_pinned = nullptr;
     bool pending_wavefront = false; uint64_t pending_paths = 0;
+    WavefrontProfile wf_prof;
 };
 
 namespace {
@@ -470,7 +471,7 @@ int rtow_render_accumulate_device(rtow_scene *s, const rtow_camera *cam, const r
     cudaStream_t st = (cudaStream_t)stream;
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTOW_N_COUNTERS * sizeof(unsigned long long), st));
     CUDA_TRY(cudaEventRecord(s->ev0, st));
-    static const int auto_kernel = [] { const char *e = getenv("RTOW_KERNEL"); return e ? atoi(e) : RTOW_KERNEL_MEGA; }();
+    static const int auto_kernel = [] { const char *e = getenv("RTOW_KERNEL"); return e ? atoi(e) : RTOW_KERNEL_WAVEFRONT; }();   // measured on B200: wavefront beats the megakernel 1.6x-4.5x on every scene
     const int kernel = params->kernel == RTOW_KERNEL_AUTO ? auto_kernel : params->kernel;
     if (kernel == RTOW_KERNEL_WAVEFRONT) {
         // Synchronises `stream` internally (the host loop polls the pool for completion).
@@ -482,7 +483,7 @@ int rtow_render_accumulate_device(rtow_scene *s, const rtow_camera *cam, const r
         if (int rc = ensure_wavefront(s, (int)pool, (size_t)n_pixels)) return rc;
         s->wf.L = L; s->wf.pool = (int)pool; s->wf.total_items = items;
         uint32_t launches = 0;
-        CUDA_TRY(run_wavefront(s->d, *cam, s->wf, d_accum, s->h_pinned, st, &launches));
+        CUDA_TRY(run_wavefront(s->d, *cam, s->wf, d_accum, s->h_pinned, st, &launches, &s->wf_prof));
         CUDA_TRY(cudaMemcpyAsync(s->d_counters, s->wf.stats, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st));
         s->pending_launches = launches;
         s->pending_wavefront = true;
@@ -535,6 +536,17 @@ int rtow_stream_stats(rtow_scene *s, void *stream, rtow_stats *stats) {
     CUDA_TRY(cudaEventElapsedTime(&stats->kernel_ms, s->ev0, s->ev1));
     stats->total_ms = stats->kernel_ms;
     stats->launches = s->pending_launches;
+    return RTOW_OK;
+}
+
+int rtow_render_profile(rtow_scene *s, rtow_render_profile_t *out) {
+    if (!s || !out) return set_error(RTOW_ERR_INVALID_ARG, "rtow_render_profile: null argument");
+    std::memset(out, 0, sizeof *out);
+    out->kernel = s->pending_wavefront ? RTOW_KERNEL_WAVEFRONT : RTOW_KERNEL_MEGA;
+    if (s->pending_wavefront) {
+        out->iterations = s->wf_prof.iterations; out->pool_slots = s->wf_prof.pool; out->sampled_iterations = s->wf_prof.samples;
+        out->extend_ms_sum = s->wf_prof.extend_ms; out->shade_ms_sum = s->wf_prof.shade_ms;
+    }
     return RTOW_OK;
 }
 

@@ -225,7 +225,8 @@ void launch_trace(const DScene &S, const rtow_ray *d_rays, uint64_t n, rtow_hit 
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         static const int minb = [] { const char *e = getenv("RTOW_TRACE_MINB"); return e ? atoi(e) : 5; }();   // tuning knob (measured on B200: 5 blocks/SM at 102 registers, no spills, beats 4, 6 and 8)
-        static const int refill = [] { const char *e = getenv("RTOW_TRACE_REFILL"); return e ? atoi(e) : RTOW_REFILL_BELOW; }();
+        static const int refill_env = [] { const char *e = getenv("RTOW_TRACE_REFILL"); return e ? atoi(e) : -1; }();
+        const int refill = refill_env >= 0 ? refill_env : (S.fast_n_nodes >= 4096 ? RTOW_REFILL_BELOW : 1);   // see run_wavefront
         static const int leaf_min = [] { const char *e = getenv("RTOW_TRACE_LEAFMIN"); return e ? atoi(e) : 8; }();
         auto go = [&](auto kern) {
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, 0);

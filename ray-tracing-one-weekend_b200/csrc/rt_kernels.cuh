@@ -44,8 +44,13 @@ struct WavefrontLaunch {
     unsigned long long *control;          // [0] next work item [1] dead slots [2] extend queue head [3] rays traced
     unsigned long long *next_item, *dead_slots, *extend_head, *stats;
 };
+// CUDA-event timings of every 8th bounce iteration that ran on a full pool (sums over `samples` iterations)
+struct WavefrontProfile {
+    float extend_ms = 0.f, shade_ms = 0.f;
+    uint32_t samples = 0, iterations = 0, pool = 0;
+};
 cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaunch &W, float *d_accum, unsigned long long *h_pinned,
-                          cudaStream_t stream, uint32_t *launches_out);
+                          cudaStream_t stream, uint32_t *launches_out, WavefrontProfile *prof);
 
 void launch_resolve(const float *d_accum, int width, int height, int spp, float *d_rgb, uint8_t *d_bgra, cudaStream_t stream);
 

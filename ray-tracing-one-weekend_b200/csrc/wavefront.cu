@@ -294,13 +294,19 @@ __global__ void wf_finalize_kernel(const unsigned long long *__restrict__ fixed,
 
 // ---- host driver ---------------------------------------------------------------------------------------------
 cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaunch &W, float *d_accum, unsigned long long *h_pinned,
-                          cudaStream_t stream, uint32_t *launches_out) {
-    static const int refill = [] { const char *e = getenv("RTOW_TRACE_REFILL"); return e ? atoi(e) : 24; }();
+                          cudaStream_t stream, uint32_t *launches_out, WavefrontProfile *prof) {
+    // Lane refill pays when traversals are long (a million spheres: ~55 node visits per ray); on a scene of a few dozen
+    // nodes a ray takes ~3 steps and the refill's load latency would dominate, so a warp then simply runs batches of 32
+    // (measured on the 101-object scene: 1.43 -> 1.95 Gpaths/s).
+    static const int refill_env = [] { const char *e = getenv("RTOW_WF_REFILL"); return e ? atoi(e) : -1; }();
+    const int refill = refill_env >= 0 ? refill_env : (S.fast_n_nodes >= 4096 ? 24 : 1);
     static const int leaf_min = [] { const char *e = getenv("RTOW_TRACE_LEAFMIN"); return e ? atoi(e) : 8; }();
     int dev = 0, sms = 148, per_sm = 4;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_extend_kernel<5>, 128, 0);
+    static const int minb = [] { const char *e = getenv("RTOW_WF_MINB"); return e ? atoi(e) : 5; }();   // tuning knob
+    if (minb >= 8) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_extend_kernel<8>, 128, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_extend_kernel<5>, 128, 0);
     const unsigned ext_blocks = (unsigned)std::min<long long>((W.pool + 127) / 128, (long long)sms * std::max(per_sm, 1));
     const unsigned pool_blocks = (unsigned)(W.pool / 256);
     const size_t n_acc = (size_t)W.L.width * W.L.height * 3;
@@ -315,21 +321,34 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
     // total_rays / pool iterations plus a tail of at most max_depth.  The dead-slot counter is read back every few
     // iterations (the reads lag the launches; extra iterations over a dead pool cost ~10 us each).
     int parity = 0;
+    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+    if (prof) { for (auto &e : ev) cudaEventCreate(&e); *prof = WavefrontProfile(); }
     for (long long it = 0;; ++it) {
-        wf_extend_kernel<5><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min);
+        const bool sampled = prof && ((it & 7) == 6 || W.total_items <= (unsigned long long)W.pool);   // timed just before a sync point
+        if (sampled) cudaEventRecord(ev[0], stream);
+        if (minb >= 8) wf_extend_kernel<8><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min);
+        else wf_extend_kernel<5><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min);
+        if (sampled) cudaEventRecord(ev[1], stream);
         wf_shade_kernel<<<pool_blocks, 256, 0, stream>>>(S, W, cam, parity);
+        if (sampled) cudaEventRecord(ev[2], stream);
         launches += 2;
         parity ^= 1;
         if ((it & 7) == 7 || W.total_items <= (unsigned long long)W.pool) {
             cudaMemcpyAsync(h_pinned, W.dead_slots, sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream);
             cudaError_t e = cudaStreamSynchronize(stream);
             if (e != cudaSuccess) return e;
+            if (prof && (it & 7) == 7 && *h_pinned == 0) {   // the sampled iteration ran on a full pool: count it
+                float a = 0.f, b = 0.f;
+                cudaEventElapsedTime(&a, ev[0], ev[1]); cudaEventElapsedTime(&b, ev[1], ev[2]);
+                prof->extend_ms += a; prof->shade_ms += b; prof->samples++;
+            }
             if (*h_pinned >= (unsigned long long)W.pool) break;
         }
     }
     wf_finalize_kernel<<<(unsigned)((n_acc + 255) / 256), 256, 0, stream>>>(W.fixed, d_accum, n_acc);
     launches++;
     if (launches_out) *launches_out = launches;
+    if (prof) { prof->iterations = (uint32_t)((launches - 2) / 2); prof->pool = (uint32_t)W.pool; for (auto &e : ev) cudaEventDestroy(e); }
     return cudaGetLastError();
 }
 
