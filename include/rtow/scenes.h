@@ -7,7 +7,7 @@
 //
 // Each consumes the global engine (rtow::api::unif01) in the same order as the reference, so
 // after rtow::api::seed(S) the flattened scene equals the flattened reference scene built
-// after randomNumberGenerator.seed(S) -- tests/test_scene_api.py checks that array by array.
+// after randomNumberGenerator.seed(S) -- tests/test_oracle_vs_reference.py checks that array by array.
 // Unused locals of the reference that allocate but never reach the scene are not reproduced
 // unless they draw random numbers (none do).
 //

@@ -1,0 +1,79 @@
+// rtow_cli.cpp -- headless front end: replaces the reference's Win32 shell (main.cpp:69-787: window, message pump,
+// worker threads, 10 000-frame loop) and winDIBbitmap.cpp's BMP dump.  Builds a scene through the scene API, renders it
+// through the C ABI on one GPU and writes the frame as PPM (8-bit, reference tone curve main.cpp:955-970) and PFM
+// (linear float), plus one JSON line of statistics.  Uses only include/rtow_b200.h + rtow_b200_scenes.h.
+//
+//   rtow_cli --scene random_ned --width 1920 --height 1080 --spp 64 --out frame [--seed 1] [--scene-seed 12345]
+//            [--depth 50] [--kernel 0|1|2] [--traverse 0|1|2] [--device 0] [--n 1000000 (bvh_stress)] [--no-wrap]
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/rtow_b200.h"
+#include "../../include/rtow_b200_scenes.h"
+
+static int fail(const char *what) {
+    std::fprintf(stderr, "rtow_cli: %s: %s\n", what, rtow_last_error());
+    return 1;
+}
+
+int main(int argc, char **argv) {
+    std::string scene = "cornell_ned", out = "frame";   // main() renders cornellBox_NED by default (main.cpp:136)
+    int W = 800, H = 800, spp = 64, depth = 50, kernel = 0, traverse = 0, device = 0, n = 0, wrap = 1;   // defines.h:7-9,27
+    unsigned long long seed = 1, scene_seed = 12345;
+    for (int i = 1; i < argc; ++i) {
+        std::string a = argv[i];
+        auto val = [&]() -> const char * { if (i + 1 >= argc) { std::fprintf(stderr, "rtow_cli: %s needs a value\n", a.c_str()); std::exit(2); } return argv[++i]; };
+        if (a == "--scene") scene = val();
+        else if (a == "--out") out = val();
+        else if (a == "--width") W = std::atoi(val());
+        else if (a == "--height") H = std::atoi(val());
+        else if (a == "--spp") spp = std::atoi(val());
+        else if (a == "--depth") depth = std::atoi(val());
+        else if (a == "--kernel") kernel = std::atoi(val());
+        else if (a == "--traverse") traverse = std::atoi(val());
+        else if (a == "--device") device = std::atoi(val());
+        else if (a == "--n") n = std::atoi(val());
+        else if (a == "--seed") seed = std::strtoull(val(), nullptr, 10);
+        else if (a == "--scene-seed") scene_seed = std::strtoull(val(), nullptr, 10);
+        else if (a == "--no-wrap") wrap = 0;
+        else { std::fprintf(stderr, "rtow_cli: unknown option %s\n", a.c_str()); return 2; }
+    }
+    if (rtow_device_count() < 1) { std::fprintf(stderr, "rtow_cli: no CUDA device (this library has no CPU path)\n"); return 3; }
+
+    rtow_host_scene *host = nullptr;
+    if (rtow_host_scene_build(scene.c_str(), scene_seed, n, wrap, &host) != RTOW_OK) return fail("scene build");
+    rtow_scene *dev = nullptr;
+    if (rtow_scene_create(rtow_host_scene_desc(host), device, &dev) != RTOW_OK) return fail("scene upload");
+
+    // the camera main() builds (main.cpp:111-125)
+    const float from[3] = {0, 0, 0}, at[3] = {1, 0, 0}, up[3] = {0, 0, -1};
+    rtow_camera cam;
+    if (rtow_host_camera(from, at, up, 60.0f, (float)W / (float)H, 2.0f, 1000.0f, 0.0f, 1.0f, &cam) != RTOW_OK) return fail("camera");
+
+    rtow_render_params p;
+    std::memset(&p, 0, sizeof p);
+    p.width = W; p.height = H; p.spp = spp; p.max_depth = depth; p.seed = seed;
+    p.global_illum_en = 1; p.sky_gain = 1.0f; p.ambient_gain = 0.3f;    // defines.h:23-25
+    p.kernel = kernel; p.traverse = traverse;
+    std::vector<float> rgb((size_t)W * H * 3);
+    std::vector<unsigned char> bgra((size_t)W * H * 4);
+    rtow_stats st;
+    if (rtow_render(dev, &cam, &p, rgb.data(), bgra.data(), &st) != RTOW_OK) return fail("render");
+    if (rtow_write_ppm((out + ".ppm").c_str(), rgb.data(), W, H) != RTOW_OK) return fail("write ppm");
+    if (rtow_write_pfm((out + ".pfm").c_str(), rgb.data(), W, H) != RTOW_OK) return fail("write pfm");
+
+    double mean = 0;
+    for (float v : rgb) mean += v;
+    mean /= (double)rgb.size();
+    std::printf("{\"scene\": \"%s\", \"width\": %d, \"height\": %d, \"spp\": %d, \"seed\": %llu, \"paths\": %llu, \"rays\": %llu, "
+                "\"kernel_ms\": %.3f, \"total_ms\": %.3f, \"launches\": %u, \"mpaths_per_s\": %.1f, \"mrays_per_s\": %.1f, "
+                "\"mean_radiance\": %.6f, \"ppm\": \"%s.ppm\", \"pfm\": \"%s.pfm\"}\n",
+                scene.c_str(), W, H, spp, seed, (unsigned long long)st.paths, (unsigned long long)st.rays, st.kernel_ms, st.total_ms, st.launches,
+                st.paths / (st.kernel_ms * 1e3), st.rays / (st.kernel_ms * 1e3), mean, out.c_str(), out.c_str());
+    rtow_scene_destroy(dev);
+    rtow_host_scene_free(host);
+    return 0;
+}

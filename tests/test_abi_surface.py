@@ -80,3 +80,13 @@ def test_product_never_touches_the_oracle():
                     if re.search(r'^\s*(from|import)\s+oracle|#include\s+"[^"]*oracle|librtow_oracle|libref_oracle|rtow_oracle_\w+\s*\(', t, flags=re.M):
                         bad.append(os.path.join(dp, fn))
     assert not bad, bad
+
+
+def test_cli_fails_loudly_without_a_device(pkg):
+    import subprocess
+    cli = os.path.join(ROOT, "ray-tracing-one-weekend_b200", "csrc", "rtow_cli")
+    assert os.path.exists(cli), "rtow_cli is built by __graft_entry__.build()"
+    if pkg.lib().rtow_device_count() > 0:
+        pytest.skip("a CUDA device is visible")
+    out = subprocess.run([cli, "--scene", "cornell_ned", "--width", "8", "--height", "8", "--spp", "1"], capture_output=True, text=True)
+    assert out.returncode == 3 and "no CPU path" in out.stderr

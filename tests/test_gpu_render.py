@@ -124,3 +124,27 @@ def test_bad_arguments_are_rejected(gpu, abi):
     with pytest.raises(gpu.RtowError):
         gpu.DeviceScene(d)
     d.abi_version = saved
+
+
+def test_headless_cli_writes_ppm_pfm_and_stats(gpu, abi, tmp_path):
+    """The headless entry that replaces the Win32 shell: PPM carries the reference tone curve of the PFM's floats."""
+    import json
+    import os
+    import subprocess
+    cli = os.path.join(os.path.dirname(gpu.lib_path()), "rtow_cli")
+    prefix = str(tmp_path / "f")
+    out = subprocess.run([cli, "--scene", "cornell_smoke_ned", "--width", "64", "--height", "36", "--spp", "8", "--seed", "5", "--out", prefix],
+                         capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    st = json.loads(out.stdout.strip().splitlines()[-1])
+    assert st["paths"] == 64 * 36 * 8 and st["rays"] > st["paths"] and st["mean_radiance"] > 0
+    pfm = open(prefix + ".pfm", "rb").read()
+    assert pfm.startswith(b"PF\n64 36\n-1.0\n")
+    rgb = np.frombuffer(pfm[len(b"PF\n64 36\n-1.0\n"):], dtype="<f4").reshape(36, 64, 3)[::-1]
+    ppm = open(prefix + ".ppm", "rb").read()
+    want = np.minimum((255.99 * np.sqrt(rgb).astype(np.float64)).astype(np.int64), 255).astype(np.uint8)
+    assert ppm[len(b"P6\n64 36\n255\n"):] == want.tobytes()
+    # the same frame through the Python binding
+    host = gpu.HostScene("cornell_smoke_ned", seed=12345)
+    img, _ = gpu.DeviceScene(host.desc).render(gpu.main_camera(64, 36), abi.default_render_params(64, 36, 8, seed=5))
+    assert np.array_equal(img, rgb)
