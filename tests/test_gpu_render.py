@@ -148,3 +148,27 @@ def test_headless_cli_writes_ppm_pfm_and_stats(gpu, abi, tmp_path):
     host = gpu.HostScene("cornell_smoke_ned", seed=12345)
     img, _ = gpu.DeviceScene(host.desc).render(gpu.main_camera(64, 36), abi.default_render_params(64, 36, 8, seed=5))
     assert np.array_equal(img, rgb)
+
+
+@pytest.mark.parametrize("kernel", ["mega", "wavefront"])
+def test_converged_image_matches_reference_golden(gpu, abi, kernel):
+    """BASELINE.json north_star: converged images must match the reference's CPU render.  tests/golden/image_*.npz holds the
+    reference's own 2048-spp moments (mt19937_64 streams); the GPU renders 4096 spp (Philox).  Gate: variance-normalised
+    z2 in (0.85, 1.15) -- i.e. the two are the same image up to Monte-Carlo noise -- and the RMSE that noise implies."""
+    import os
+    from golden_spec import IMAGE_CASES
+    from test_oracle_golden import reference_earth, z2_statistic, load
+    for name, kw, (W, H, ref_spp) in IMAGE_CASES:
+        g = load(f"image_{name}.npz")
+        host = gpu.HostScene(name, seed=12345, wrap=True, image=reference_earth())
+        dev = gpu.DeviceScene(host.desc)
+        spp = 4096
+        p = abi.default_render_params(W, H, spp, seed=1234, kernel=abi.KERNEL_MEGA if kernel == "mega" else abi.KERNEL_WAVEFRONT)
+        img, st = dev.render(gpu.main_camera(W, H), p)
+        z2, flat = z2_statistic(img.astype(np.float64), spp, g["mean"].astype(np.float64), g["var"].astype(np.float64), int(g["spp"]))
+        rmse = float(np.sqrt(np.mean((img - g["mean"]) ** 2)))
+        expected = float(np.sqrt(np.mean(g["var"] * (1.0 / spp + 1.0 / int(g["spp"])))))
+        print(f"{name}/{kernel}: z2 {z2:.3f}, RMSE {rmse:.4f} (noise floor {expected:.4f}), rays/path {st.rays / st.paths:.3f} vs {float(g['rays_per_path']):.3f}")
+        assert 0.85 < z2 < 1.15, f"{name}: z2 = {z2}"
+        assert flat < 1e-3 and rmse < 1.15 * expected
+        assert abs(st.rays / st.paths - float(g["rays_per_path"])) < 0.01 * float(g["rays_per_path"])
