@@ -235,20 +235,20 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
     B.nodes.reserve((size_t)2 * n);
     int broot = B.build(0, n);
 
-    // collapse to 4-wide, depth first
+    // collapse to 4-wide, depth first, into wide nodes with float boxes; they are quantised afterwards
     const double pad_rel = 4e-7;
+    struct Wide { float lo[3][4], hi[3][4]; int32_t ref[4]; int nk; };
+    std::vector<Wide> wide;
+    wide.reserve((size_t)n / 2 + 1);
     struct Item { int bnode; int slot_node; int slot; int depth; };
-    out.nodes.clear();
-    out.nodes.reserve((size_t)n / 2 * FAST_NODE_F4);
     std::vector<Item> stack;
     auto new_node = [&]() {
-        int id = (int)(out.nodes.size() / FAST_NODE_F4);
-        for (int k = 0; k < FAST_NODE_F4; ++k) out.nodes.push_back(make_float4(0, 0, 0, 0));
-        float4 &refs = out.nodes[(size_t)id * FAST_NODE_F4 + 6];
-        refs = make_float4(i2f(FAST_EMPTY), i2f(FAST_EMPTY), i2f(FAST_EMPTY), i2f(FAST_EMPTY));
-        return id;
+        Wide w;
+        std::memset(&w, 0, sizeof w);
+        for (int k = 0; k < 4; ++k) w.ref[k] = FAST_EMPTY;
+        wide.push_back(w);
+        return (int)wide.size() - 1;
     };
-    auto set_lane = [](float4 &v, int k, float x) { (k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w) = x; };
     out.root = new_node();
     stack.push_back({broot, -1, -1, 1});
     out.max_depth = 1;
@@ -260,7 +260,7 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
         if (first) { id = out.root; first = false; }
         else {
             id = new_node();
-            set_lane(out.nodes[(size_t)it.slot_node * FAST_NODE_F4 + 6], it.slot, i2f(id));
+            wide[it.slot_node].ref[it.slot] = id;
         }
         int kids[4]; int nk = 0;
         const BNode &bn = B.nodes[it.bnode];
@@ -279,17 +279,62 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
                 kids[nk++] = B.nodes[c].right;
             }
         }
+        wide[id].nk = nk;
         for (int k = 0; k < nk; ++k) {
             const BNode &c = B.nodes[kids[k]];
-            float4 *nd = &out.nodes[(size_t)id * FAST_NODE_F4];
             for (int a = 0; a < 3; ++a) {
                 double pad = pad_rel * (ext + std::fabs(c.box.lo[a]) + std::fabs(c.box.hi[a])) + 1e-30;
-                set_lane(nd[2 * a], k, down(c.box.lo[a], pad));
-                set_lane(nd[2 * a + 1], k, up(c.box.hi[a], pad));
+                wide[id].lo[a][k] = down(c.box.lo[a], pad);
+                wide[id].hi[a][k] = up(c.box.hi[a], pad);
             }
-            if (c.obj >= 0) set_lane(nd[6], k, i2f(leaf_ref[c.obj]));
+            if (c.obj >= 0) wide[id].ref[k] = leaf_ref[c.obj];
             else stack.push_back({kids[k], id, k, it.depth + 1});
         }
+    }
+
+    // Quantise: per node an origin p (float) and a power-of-two cell size 2^e per axis; child planes are bytes on that
+    // grid, lo rounded down and hi rounded up, so the decoded box contains the float box (culling stays conservative).
+    out.nodes.assign(wide.size() * FAST_NODE_F4, make_float4(0, 0, 0, 0));
+    for (size_t id = 0; id < wide.size(); ++id) {
+        const Wide &w = wide[id];
+        float p[3]; uint32_t ebyte[3]; uint32_t qlo[3] = {0, 0, 0}, qhi[3] = {0, 0, 0};
+        for (int a = 0; a < 3; ++a) {
+            float mn = FLT_MAX, mx = -FLT_MAX;
+            for (int k = 0; k < w.nk; ++k) { mn = std::min(mn, w.lo[a][k]); mx = std::max(mx, w.hi[a][k]); }
+            if (w.nk == 0) { mn = mx = 0.f; }
+            p[a] = mn;
+            int e = -126;
+            double extent = (double)mx - (double)mn;
+            if (extent > 0) {
+                e = (int)std::ceil(std::log2(extent / 255.0));
+                if (e < -126) e = -126;
+            }
+            for (;; ++e) {     // raise e until every hi plane fits in a byte (and the grid sums are exact enough)
+                if (e > 127) return fail("box extent too large to quantise");
+                const double cell = std::ldexp(1.0, e);
+                bool ok = true;
+                for (int k = 0; k < w.nk && ok; ++k) ok = std::ceil(((double)w.hi[a][k] - (double)mn) / cell) <= 255.0;
+                if (ok) break;
+            }
+            const double cell = std::ldexp(1.0, e);
+            ebyte[a] = (uint32_t)(e + 127);
+            for (int k = 0; k < 4; ++k) {
+                uint32_t lo_q = 255, hi_q = 0;     // empty slot: inverted interval
+                if (k < w.nk) {
+                    double l = std::floor(((double)w.lo[a][k] - (double)mn) / cell), h = std::ceil(((double)w.hi[a][k] - (double)mn) / cell);
+                    // the kernel evaluates p + q*cell in float: step outward until the float value is on the safe side
+                    while (l > 0 && (double)(float)((double)mn + l * cell) > (double)w.lo[a][k]) l -= 1;
+                    while (h < 255 && (double)(float)((double)mn + h * cell) < (double)w.hi[a][k]) h += 1;
+                    lo_q = (uint32_t)std::max(0.0, std::min(255.0, l)); hi_q = (uint32_t)std::max(0.0, std::min(255.0, h));
+                }
+                qlo[a] |= lo_q << (8 * k); qhi[a] |= hi_q << (8 * k);
+            }
+        }
+        float4 *nd = &out.nodes[id * FAST_NODE_F4];
+        nd[0] = make_float4(p[0], p[1], p[2], i2f((int32_t)(ebyte[0] | ebyte[1] << 8 | ebyte[2] << 16)));
+        nd[1] = make_float4(i2f((int32_t)qlo[0]), i2f((int32_t)qlo[1]), i2f((int32_t)qlo[2]), i2f((int32_t)qhi[0]));
+        nd[2] = make_float4(i2f((int32_t)qhi[1]), i2f((int32_t)qhi[2]), 0.f, 0.f);
+        nd[3] = make_float4(i2f(w.ref[0]), i2f(w.ref[1]), i2f(w.ref[2]), i2f(w.ref[3]));
     }
     return true;
 }

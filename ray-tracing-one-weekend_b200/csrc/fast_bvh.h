@@ -20,15 +20,18 @@
 
 namespace rtow {
 
-// Node = 8 x float4 (128 B, one cache line):
-//   [0] lo.x of the 4 children  [1] hi.x  [2] lo.y  [3] hi.y  [4] lo.z  [5] hi.z
-//   [6] child refs as int bits: >= 0 node index; < 0 leaf, ~ref = object id | FAST_LEAF_* flags;
-//       FAST_EMPTY = no child
-//   [7] unused
+// Node = 4 x float4 (64 B, half a cache line, fetched with two 256-bit loads), child boxes quantised to bytes on a
+// per-node grid (after Ylitie, Karras, Laine 2017 "Efficient incoherent ray traversal on GPUs through compressed wide
+// BVHs"): a lane that is alone on its node pays one L1 wavefront per load instruction, so bytes per node are what the
+// closest-hit kernel is bound by.  Decoded boxes contain the float boxes (lo rounded down, hi up): culling only.
+//   [0] origin p.xyz (float), exponent bytes ex | ey << 8 | ez << 16 (biased: cell size = 2^(e-127))
+//   [1] lo.x, lo.y, lo.z, hi.x   each word = the 4 children's bytes (child k in bits 8k..8k+7)
+//   [2] hi.y, hi.z, -, -
+//   [3] child refs as int bits: >= 0 node index; < 0 leaf, ~ref = object id | FAST_LEAF_* flags; FAST_EMPTY = no child
 // Per object (leaf), indexed by object id:
 //   spheres[obj]        {cx,cy,cz,r} of a bare Sphere leaf (FAST_LEAF_SPHERE), else zeros
 //   guards[2*obj..+1]   {bmin.xyz, -} {bmax.xyz, -}: box of the reference BvhNode that owns the leaf
-enum { FAST_NODE_F4 = 8 };
+enum { FAST_NODE_F4 = 4 };
 static const int32_t FAST_EMPTY = 0x7fffffff;
 enum {
     FAST_LEAF_SPHERE = 1 << 30,   // the object is one untransformed Sphere: test spheres[obj] directly

@@ -51,6 +51,11 @@ __device__ __forceinline__ float4 sel4(bool c, const float4 &a, const float4 &b)
     return make_float4(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z, c ? a.w : b.w);
 }
 
+// byte k of w as a float, on the integer/FP32 pipes (no I2F): 0x4B0000qq is 2^23 + q exactly
+__device__ __forceinline__ float byte_f(unsigned w, int k) {
+    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440 + k)) - 8388608.0f;
+}
+
 __device__ __forceinline__ float lane4(const float4 &v, int k) { return k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w; }
 
 __device__ __forceinline__ bool fast_covers(const DScene &S, const Ray &r, float tmin, float tmax) {
@@ -130,30 +135,36 @@ __device__ __forceinline__ bool fast_at_leaf(const FastTrav &T) { return T.cur <
 template <bool COUNT, class STACK>
 __device__ __forceinline__ void fast_node(const DScene &S, FastTrav &T, STACK &st, unsigned &node_visits) {
     if (COUNT) node_visits++;
-    // A node is one 128 B line; a lane that is alone on its node pays one L1 wavefront per load instruction, so the
-    // line is fetched with four 256-bit loads (LDG.E.256, sm_100+) instead of seven 128-bit ones.
+    // 64-byte quantised node (fast_bvh.h), two 256-bit loads
     const float4 *nd = S.fast_nodes + (size_t)T.cur * FAST_NODE_F4;
-    float4 lox, hix, loy, hiy, loz, hiz, rf, unused;
-    ldg256(nd, lox, hix); ldg256(nd + 2, loy, hiy); ldg256(nd + 4, loz, hiz); ldg256(nd + 6, rf, unused);
+    float4 q0, q1, q2, q3;
+    ldg256(nd, q0, q1); ldg256(nd + 2, q2, q3);
+    const unsigned ex = __float_as_uint(q0.w);
+    // plane t = q * (cell * 1/d) + (p - o) * 1/d, per axis
+    const float ax = __uint_as_float((ex & 0xffu) << 23) * T.ix, ay = __uint_as_float((ex & 0xff00u) << 15) * T.iy,
+                az = __uint_as_float((ex & 0xff0000u) << 7) * T.iz;
+    const float bx = fmaf(q0.x, T.ix, -T.pox), by = fmaf(q0.y, T.iy, -T.poy), bz = fmaf(q0.z, T.iz, -T.poz);
     const bool sx = T.ix < 0.f, sy = T.iy < 0.f, sz = T.iz < 0.f;
-    const float4 nx = sel4(sx, hix, lox), fx = sel4(sx, lox, hix);
-    const float4 ny = sel4(sy, hiy, loy), fy = sel4(sy, loy, hiy);
-    const float4 nz = sel4(sz, hiz, loz), fz = sel4(sz, loz, hiz);
+    const unsigned lox = __float_as_uint(q1.x), loy = __float_as_uint(q1.y), loz = __float_as_uint(q1.z);
+    const unsigned hix = __float_as_uint(q1.w), hiy = __float_as_uint(q2.x), hiz = __float_as_uint(q2.y);
+    const unsigned wnx = sx ? hix : lox, wfx = sx ? lox : hix;     // near / far plane bytes of the 4 children
+    const unsigned wny = sy ? hiy : loy, wfy = sy ? loy : hiy;
+    const unsigned wnz = sz ? hiz : loz, wfz = sz ? loz : hiz;
     const float aix = fabsf(T.ix), aiy = fabsf(T.iy), aiz = fabsf(T.iz);
     const float ub = T.bestc * 1.000001f;
     const float inf = __int_as_float(0x7f800000);
     float d[4]; int ref[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        // plane distances of the un-inflated child box
-        const float nxk = fmaf(lane4(nx, k), T.ix, -T.pox), nyk = fmaf(lane4(ny, k), T.iy, -T.poy), nzk = fmaf(lane4(nz, k), T.iz, -T.poz);
-        const float fxk = fmaf(lane4(fx, k), T.ix, -T.pox), fyk = fmaf(lane4(fy, k), T.iy, -T.poy), fzk = fmaf(lane4(fz, k), T.iz, -T.poz);
+        // plane distances of the (decoded) child box
+        const float nxk = fmaf(byte_f(wnx, k), ax, bx), nyk = fmaf(byte_f(wny, k), ay, by), nzk = fmaf(byte_f(wnz, k), az, bz);
+        const float fxk = fmaf(byte_f(wfx, k), ax, bx), fyk = fmaf(byte_f(wfy, k), ay, by), fzk = fmaf(byte_f(wfz, k), az, bz);
         // exit distance under the ray's current slack bounds every accepted t in this child -> the child's own slack
         const float tf0 = fminf(fminf(fmaf(T.eta, aix, fxk), fmaf(T.eta, aiy, fyk)), fminf(fmaf(T.eta, aiz, fzk), ub));
         const float ek = fminf(T.eta, fmaf(T.Kd, fmaxf(tf0, 0.f) * 1.000001f, T.base));
         const float tn = fmaxf(fmaxf(fmaf(-ek, aix, nxk), fmaf(-ek, aiy, nyk)), fmaxf(fmaf(-ek, aiz, nzk), T.tmin));
         const float tf = fminf(fminf(fmaf(ek, aix, fxk), fmaf(ek, aiy, fyk)), fminf(fmaf(ek, aiz, fzk), ub));
-        ref[k] = __float_as_int(lane4(rf, k));
+        ref[k] = __float_as_int(lane4(q3, k));
         d[k] = (tn <= tf && ref[k] != FAST_EMPTY) ? tn : inf;
     }
     // sort ascending by entry distance (5-comparator network)
@@ -204,7 +215,8 @@ __device__ __forceinline__ void fast_leaf(const DScene &S, FastTrav &T, const Rn
         Rng g;
         rng_init(g, key.seed, key.pixel, key.sample);
         g.bounce = key.bounce;
-        h = fast_object_leaf<COUNT>(S, T.r, T.tmin, T.tmax, &g, obj, code & FAST_LEAF_TWICE, t, pid, prim_tests);
+        const Ray rr = T.r;      // a copy for the out-of-line call: taking T.r's address would pin the whole state in local memory
+        h = fast_object_leaf<COUNT>(S, rr, T.tmin, T.tmax, &g, obj, code & FAST_LEAF_TWICE, t, pid, prim_tests);
     }
     if (h && (t < T.best || (t == T.best && obj > T.best_obj))) {
         const float4 g0 = __ldg(S.fast_guards + 2 * (size_t)obj), g1 = __ldg(S.fast_guards + 2 * (size_t)obj + 1);
