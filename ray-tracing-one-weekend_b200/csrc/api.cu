@@ -8,6 +8,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <map>
 #include <vector>
 
 #include "errors.h"
@@ -302,7 +303,32 @@ int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out)
 
     int rc;
     static_assert(sizeof(rtow_prim) == 80 && sizeof(rtow_xform) == 16, "POD layout");
-    if ((rc = upload(s, (const int4 *)desc->prims, (size_t)desc->n_prims * 5, &D.prims))) return rc;
+    {   // device copy of the primitives: xform_count shares its word with the ray-chain key (rt_device.cuh RayCache).
+        // Two primitives get the same key exactly when their Translate/RotateY sequences are equal value for value
+        // (FlipNormals does not move the ray), so a run of them can reuse one transformed ray.
+        std::vector<rtow_prim> dp(desc->prims, desc->prims + desc->n_prims);
+        std::map<std::vector<uint32_t>, int> key_of;
+        std::vector<uint32_t> sig;
+        for (auto &p : dp) {
+            if (p.xform_count > 255) return set_error(RTOW_ERR_UNSUPPORTED, "a wrapper chain longer than 255 is not supported");
+            sig.clear();
+            for (int i = p.xform_begin; i < p.xform_begin + p.xform_count; ++i) {
+                const rtow_xform &x = desc->xforms[i];
+                if (x.type != RTOW_XF_TRANSLATE && x.type != RTOW_XF_ROTATE_Y) continue;
+                uint32_t w[3]; std::memcpy(w, x.f, 12);
+                sig.push_back((uint32_t)x.type); sig.insert(sig.end(), w, w + 3);
+            }
+            int key = 0;
+            if (!sig.empty()) {
+                auto it = key_of.find(sig);
+                if (it != key_of.end()) key = it->second;
+                else if (key_of.size() + 1 < RTOW_RAY_KEY_NONE) key = key_of[sig] = (int)key_of.size() + 1;
+                else key = RTOW_RAY_KEY_NONE;
+            }
+            p.xform_count |= key << 8;
+        }
+        if ((rc = upload(s, (const int4 *)dp.data(), (size_t)desc->n_prims * 5, &D.prims))) return rc;
+    }
     if ((rc = upload(s, (const float4 *)desc->xforms, (size_t)desc->n_xforms, &D.xforms))) return rc;
 
     std::vector<int4> objs(desc->n_objects);

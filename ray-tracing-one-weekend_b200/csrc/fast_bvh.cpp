@@ -293,7 +293,11 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
     }
 
     // Quantise: per node an origin p (float) and a power-of-two cell size 2^e per axis; child planes are bytes on that
-    // grid, lo rounded down and hi rounded up, so the decoded box contains the float box (culling stays conservative).
+    // grid.  The kernel turns a byte q into the float 32768 + q with one byte permute (rt_fast.cuh byte_f), so the
+    // stored origin is p - 32768 cells and a plane is  stored_origin + (32768 + q) * cell.  In the kernel's ray-space
+    // form of that sum the two large terms cancel, leaving roundings of up to ~cell/256; every plane is therefore
+    // placed at least cell/64 outside the float box (lo down, hi up): the decoded box contains the float box with
+    // that margin and culling stays conservative.
     out.nodes.assign(wide.size() * FAST_NODE_F4, make_float4(0, 0, 0, 0));
     for (size_t id = 0; id < wide.size(); ++id) {
         const Wide &w = wide[id];
@@ -302,31 +306,33 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
             float mn = FLT_MAX, mx = -FLT_MAX;
             for (int k = 0; k < w.nk; ++k) { mn = std::min(mn, w.lo[a][k]); mx = std::max(mx, w.hi[a][k]); }
             if (w.nk == 0) { mn = mx = 0.f; }
-            p[a] = mn;
-            int e = -126;
+            int e = -100;
             double extent = (double)mx - (double)mn;
             if (extent > 0) {
-                e = (int)std::ceil(std::log2(extent / 255.0));
-                if (e < -126) e = -126;
+                e = (int)std::ceil(std::log2(extent / 254.0));
+                if (e < -100) e = -100;
             }
-            for (;; ++e) {     // raise e until every hi plane fits in a byte (and the grid sums are exact enough)
-                if (e > 127) return fail("box extent too large to quantise");
-                const double cell = std::ldexp(1.0, e);
-                bool ok = true;
-                for (int k = 0; k < w.nk && ok; ++k) ok = std::ceil(((double)w.hi[a][k] - (double)mn) / cell) <= 255.0;
-                if (ok) break;
+            uint32_t lq[4], hq[4];
+            for (;; ++e) {     // raise e until every plane, with its margin, fits in a byte
+                if (e > 100) return fail("box extent too large to quantise");
+                const double cell = std::ldexp(1.0, e), margin = cell / 64.0;
+                const float pf = (float)((double)mn - cell / 32.0 - 32768.0 * cell);
+                const double origin = (double)pf + 32768.0 * cell;      // where byte 0 decodes to
+                bool ok = std::isfinite(pf);
+                for (int k = 0; k < w.nk && ok; ++k) {
+                    double l = std::floor(((double)w.lo[a][k] - margin - origin) / cell);
+                    double h = std::ceil(((double)w.hi[a][k] + margin - origin) / cell);
+                    while (origin + l * cell > (double)w.lo[a][k] - margin) l -= 1;
+                    while (origin + h * cell < (double)w.hi[a][k] + margin) h += 1;
+                    ok = l >= 0 && h <= 255;
+                    lq[k] = (uint32_t)l; hq[k] = (uint32_t)h;
+                }
+                if (ok) { p[a] = pf; break; }
             }
-            const double cell = std::ldexp(1.0, e);
             ebyte[a] = (uint32_t)(e + 127);
             for (int k = 0; k < 4; ++k) {
                 uint32_t lo_q = 255, hi_q = 0;     // empty slot: inverted interval
-                if (k < w.nk) {
-                    double l = std::floor(((double)w.lo[a][k] - (double)mn) / cell), h = std::ceil(((double)w.hi[a][k] - (double)mn) / cell);
-                    // the kernel evaluates p + q*cell in float: step outward until the float value is on the safe side
-                    while (l > 0 && (double)(float)((double)mn + l * cell) > (double)w.lo[a][k]) l -= 1;
-                    while (h < 255 && (double)(float)((double)mn + h * cell) < (double)w.hi[a][k]) h += 1;
-                    lo_q = (uint32_t)std::max(0.0, std::min(255.0, l)); hi_q = (uint32_t)std::max(0.0, std::min(255.0, h));
-                }
+                if (k < w.nk) { lo_q = lq[k]; hi_q = hq[k]; }
                 qlo[a] |= lo_q << (8 * k); qhi[a] |= hi_q << (8 * k);
             }
         }

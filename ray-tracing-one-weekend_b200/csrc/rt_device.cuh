@@ -206,18 +206,32 @@ __device__ __forceinline__ bool rect_t(float lo0, float hi0, float lo1, float hi
 
 struct PrimHead {
     int type, mat_id, xf_begin, xf_count;
+    int ray_key;      // equal keys <=> equal Translate/RotateY sequences (FlipNormals ignored); 0 = none.  See api.cu.
 };
+#define RTOW_RAY_KEY_NONE 0xffffff      // no key assigned: always transform
 
 __device__ __forceinline__ PrimHead load_head(const int4 *__restrict__ prims, int pid) {
     int4 h = __ldg(&prims[pid * 5]);
-    PrimHead p; p.type = h.x; p.mat_id = h.y; p.xf_begin = h.z; p.xf_count = h.w;
+    PrimHead p; p.type = h.x; p.mat_id = h.y; p.xf_begin = h.z; p.xf_count = h.w & 0xff; p.ray_key = (int)((unsigned)h.w >> 8);
     return p;
 }
 
+// The ray of the enclosing scope moved into a primitive's space, remembered across the primitives of one run: the six
+// rectangles of a Box behind Translate(RotateY(.)) share one chain, and a medium asks for its boundary twice.
+struct RayCache {
+    int key;
+    Ray r;
+};
+__device__ __forceinline__ void ray_cache_reset(RayCache &c, const Ray &r_in) { c.key = 0; c.r = r_in; }
+
 // One non-medium primitive behind its wrapper chain; r_in is in the enclosing aggregate's space.
-__device__ __forceinline__ bool simple_prim_t(const DScene &S, int pid, const PrimHead &p, const Ray &r_in, float tmin, float tmax, float &t_out) {
-    Ray r = r_in;
-    chain_ray(S.xforms, p.xf_begin, p.xf_count, r);
+__device__ __forceinline__ bool simple_prim_t(const DScene &S, int pid, const PrimHead &p, const Ray &r_in, RayCache &rc, float tmin, float tmax,
+                                              float &t_out) {
+    if (p.ray_key != rc.key || p.ray_key == RTOW_RAY_KEY_NONE) {
+        rc.r = r_in; rc.key = p.ray_key;
+        chain_ray(S.xforms, p.xf_begin, p.xf_count, rc.r);
+    }
+    const Ray &r = rc.r;
     const float4 *f = reinterpret_cast<const float4 *>(S.prims + pid * 5 + 1);
     float4 f0 = __ldg(&f[0]);
     if (p.type == RTOW_PRIM_SPHERE) return sphere_t(f0.x, f0.y, f0.z, f0.w, r, tmin, tmax, t_out);
@@ -235,13 +249,13 @@ __device__ __forceinline__ bool simple_prim_t(const DScene &S, int pid, const Pr
 }
 
 // hitableList.h:20-38 over a run of non-medium primitives (a medium's boundary)
-__device__ __forceinline__ bool run_hit_simple(const DScene &S, int begin, int count, const Ray &r, float tmin, float tmax, float &t_out) {
+__device__ __forceinline__ bool run_hit_simple(const DScene &S, int begin, int count, const Ray &r, RayCache &rc, float tmin, float tmax, float &t_out) {
     bool any = false;
     float closest = tmax;
     for (int i = begin; i < begin + count; ++i) {
         PrimHead p = load_head(S.prims, i);
         float t;
-        if (simple_prim_t(S, i, p, r, tmin, closest, t)) { any = true; closest = t; t_out = t; }
+        if (simple_prim_t(S, i, p, r, rc, tmin, closest, t)) { any = true; closest = t; t_out = t; }
     }
     return any;
 }
@@ -254,9 +268,16 @@ __device__ __forceinline__ bool medium_t(const DScene &S, int pid, const PrimHea
     float density = __int_as_float(__ldg(&S.prims[pid * 5 + 1]).x);
     int4 tail = __ldg(&S.prims[pid * 5 + 4]);
     int cb = tail.x, cn = tail.y;
-    float t1, t2;
-    if (!run_hit_simple(S, cb, cn, r, -FLT_MAX, FLT_MAX, t1)) return false;
-    if (!run_hit_simple(S, cb, cn, r, (float)((double)t1 + 0.0001), FLT_MAX, t2)) return false;
+    float t1 = 0.f, t2 = 0.f;
+    RayCache rc;
+    ray_cache_reset(rc, r);
+    float from = -FLT_MAX;
+#pragma unroll 1      // one copy of the boundary test in the instruction stream (the traversal kernels are I-cache bound)
+    for (int pass = 0; pass < 2; ++pass) {
+        float t;
+        if (!run_hit_simple(S, cb, cn, r, rc, from, FLT_MAX, t)) return false;
+        if (pass == 0) { t1 = t; from = (float)((double)t1 + 0.0001); } else t2 = t;
+    }
     if (t1 < tmin) t1 = tmin;
     if (t2 > tmax) t2 = tmax;
     if (t1 >= t2) return false;
@@ -276,13 +297,30 @@ __device__ __forceinline__ bool run_hit(const DScene &S, int begin, int count, c
     bool any = false;
     float closest = tmax;
     if (COUNT) prim_tests += (unsigned)count;
+    RayCache rc;
+    ray_cache_reset(rc, r);
     for (int i = begin; i < begin + count; ++i) {
         PrimHead p = load_head(S.prims, i);
         float t;
-        bool h = (p.type == RTOW_PRIM_MEDIUM) ? medium_t(S, i, p, r, tmin, closest, g, visit, t) : simple_prim_t(S, i, p, r, tmin, closest, t);
+        bool h = (p.type == RTOW_PRIM_MEDIUM) ? medium_t(S, i, p, r, tmin, closest, g, visit, t) : simple_prim_t(S, i, p, r, rc, tmin, closest, t);
         if (h) { any = true; closest = t; t_out = t; prim_out = i; }
     }
     return any;
+}
+
+// One top-level object (a run of primitives), evaluated `visits` times as an n == 1 BvhNode does
+// (left.t < right.t ? left : right, bvhNode.h:74-77).  Out of line and shared by both traversals: one copy of the
+// primitive code per kernel.  The ray comes by value so that callers keep theirs in registers.
+template <bool COUNT>
+__device__ __noinline__ bool object_hit(const DScene &S, const Ray r, float tmin, float tmax, const Rng *g, int begin, int count, int visit0,
+                                        int visits, float &t, int &pid, unsigned &prim_tests) {
+    bool h = false;
+#pragma unroll 1
+    for (int v = 0; v < visits; ++v) {
+        float t2; int pid2;
+        if (run_hit<COUNT>(S, begin, count, r, tmin, tmax, g, visit0 + v, t2, pid2, prim_tests) && !(h && t < t2)) { h = true; t = t2; pid = pid2; }
+    }
+    return h;
 }
 
 // ---- closest hit, EXACT: the reference tree as is -- box test, then BOTH children with the
@@ -290,7 +328,7 @@ __device__ __forceinline__ bool run_hit(const DScene &S, int begin, int count, c
 template <bool COUNT>
 __device__ __forceinline__ bool closest_hit_exact(const DScene &S, const Ray &r, float tmin, float tmax, const Rng *g, float &t_out, int &prim_out,
                                                   unsigned &node_visits, unsigned &prim_tests) {
-    if (S.top_kind != RTOW_TOP_BVH) return run_hit<COUNT>(S, 0, S.n_prims_top, r, tmin, tmax, g, 0, t_out, prim_out, prim_tests);
+    if (S.top_kind != RTOW_TOP_BVH) return object_hit<COUNT>(S, r, tmin, tmax, g, 0, S.n_prims_top, 0, 1, t_out, prim_out, prim_tests);
     float best = __int_as_float(0x7f800000);
     int best_prim = -1;
     int i = 0;
@@ -310,7 +348,7 @@ __device__ __forceinline__ bool closest_hit_exact(const DScene &S, const Ray &r,
                 h = sphere_t(a.x, a.y, a.z, a.w, r, tmin, tmax, t);
             } else {
                 int4 o = __ldg(&S.objects[__float_as_int(b.x)]);
-                h = run_hit<COUNT>(S, o.x, o.y, r, tmin, tmax, g, __float_as_int(b.y), t, pid, prim_tests);
+                h = object_hit<COUNT>(S, r, tmin, tmax, g, o.x, o.y, __float_as_int(b.y), 1, t, pid, prim_tests);
             }
             if (h && t <= best) { best = t; best_prim = pid; }
             i++;

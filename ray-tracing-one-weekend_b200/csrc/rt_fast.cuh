@@ -51,9 +51,11 @@ __device__ __forceinline__ float4 sel4(bool c, const float4 &a, const float4 &b)
     return make_float4(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z, c ? a.w : b.w);
 }
 
-// byte k of w as a float, on the integer/FP32 pipes (no I2F): 0x4B0000qq is 2^23 + q exactly
+// byte k of w as the float 32768 + q, with one PRMT (no I2F, no subtraction): 0x4700qq00 is 2^15 + q exactly.  The
+// builder folds the -32768 cells into the stored node origin (fast_bvh.cpp) and widens every plane by cell/64, which
+// covers the cell/512-sized roundings this leaves in the plane distances.
 __device__ __forceinline__ float byte_f(unsigned w, int k) {
-    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440 + k)) - 8388608.0f;
+    return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7404 + (k << 4)));
 }
 
 __device__ __forceinline__ float lane4(const float4 &v, int k) { return k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w; }
@@ -105,6 +107,14 @@ struct LocalStack {
     __device__ __forceinline__ void put(int i, int r, float dist) { ref[i] = r; d[i] = dist; }
     __device__ __forceinline__ float dist(int i) const { return d[i]; }
     __device__ __forceinline__ int node(int i) const { return ref[i]; }
+    // entries 1..3 of a sorted child list (d1 <= d2 <= d3, culled ones = +inf), pushed far-to-near
+    __device__ __forceinline__ int push3(int sp, const int *r, const float *dd) {
+        const float inf = __int_as_float(0x7f800000);
+        if (dd[3] < inf) put(sp++, r[3], dd[3]);
+        if (dd[2] < inf) put(sp++, r[2], dd[2]);
+        if (dd[1] < inf) put(sp++, r[1], dd[1]);
+        return sp;
+    }
 };
 template <int CAP>
 struct SmemStack {
@@ -117,6 +127,24 @@ struct SmemStack {
     }
     __device__ __forceinline__ float dist(int i) const { return i < CAP ? sd[i * 32] : ld[i - CAP]; }
     __device__ __forceinline__ int node(int i) const { return i < CAP ? sref[i * 32] : lref[i - CAP]; }
+    // Branch-free in the common case (all three slots in shared memory): every candidate is stored, and the slot index
+    // only advances past the live ones -- a culled entry (they sort last) is overwritten by the next store.
+    __device__ __forceinline__ int push3(int sp, const int *r, const float *dd) {
+        const float inf = __int_as_float(0x7f800000);
+        if (sp + 3 <= CAP) {
+            int *pr = sref + sp * 32; float *pd = sd + sp * 32;
+            pr[0] = r[3]; pd[0] = dd[3];
+            int k = dd[3] < inf ? 32 : 0;
+            pr[k] = r[2]; pd[k] = dd[2];
+            k += dd[2] < inf ? 32 : 0;
+            pr[k] = r[1]; pd[k] = dd[1];
+            return sp + (k >> 5) + (dd[1] < inf ? 1 : 0);
+        }
+        if (dd[3] < inf) put(sp++, r[3], dd[3]);
+        if (dd[2] < inf) put(sp++, r[2], dd[2]);
+        if (dd[1] < inf) put(sp++, r[1], dd[1]);
+        return sp;
+    }
 };
 
 // One pop attempt: the next stacked subtree if it can still hold a hit with t <= best, else stay in POP state.
@@ -176,24 +204,8 @@ __device__ __forceinline__ void fast_node(const DScene &S, FastTrav &T, STACK &s
     }
     RTOW_CSWAP(0, 1) RTOW_CSWAP(2, 3) RTOW_CSWAP(0, 2) RTOW_CSWAP(1, 3) RTOW_CSWAP(1, 2)
 #undef RTOW_CSWAP
-    if (d[3] < inf) { st.put(T.sp, ref[3], d[3]); T.sp++; }
-    if (d[2] < inf) { st.put(T.sp, ref[2], d[2]); T.sp++; }
-    if (d[1] < inf) { st.put(T.sp, ref[1], d[1]); T.sp++; }
+    T.sp = st.push3(T.sp, ref, d);
     T.cur = d[0] < inf ? ref[0] : RTOW_TRAV_POP;
-}
-
-// A leaf that is not a bare sphere: a run of primitives (Box, MovingSphere, wrapped objects, media).  Kept out of line:
-// the hot loop of the big-BVH case never comes here.
-template <bool COUNT>
-__device__ __noinline__ bool fast_object_leaf(const DScene &S, const Ray &r, float tmin, float tmax, const Rng *g, int obj, int twice, float &t,
-                                              int &pid, unsigned &prim_tests) {
-    const int4 o = __ldg(&S.objects[obj]);
-    bool h = run_hit<COUNT>(S, o.x, o.y, r, tmin, tmax, g, 0, t, pid, prim_tests);
-    if (twice) {   // n == 1 node: left.t < right.t ? left : right  (bvhNode.h:74-77)
-        float t2; int pid2;
-        if (run_hit<COUNT>(S, o.x, o.y, r, tmin, tmax, g, 1, t2, pid2, prim_tests) && !(h && t < t2)) { h = true; t = t2; pid = pid2; }
-    }
-    return h;
 }
 
 // Where the per-path counter of a medium's free-flight draw comes from (rng_medium): built only if a medium is met.
@@ -201,6 +213,21 @@ struct RngKey {
     uint64_t seed;
     uint32_t pixel, sample, bounce;
 };
+
+// Sufficient condition for AABB::hit(guard box, tmin, tmax) (aabb.h:22-43) to pass, in cheap arithmetic: if the hit
+// parameter t lies strictly inside every slab interval with a margin far above the rounding of either arithmetic
+// (1e-5 relative + the ray's coordinate-rounding term), then the reference's running tmin/tmax stay on either side of
+// t after every axis and the test returns true.  Almost every candidate passes here; the rest (hits within the margin
+// of a guard face) take the reference's division-form test (6 IEEE divisions) as before.
+__device__ __forceinline__ bool guard_surely_passes(const float4 &g0, const float4 &g1, const FastTrav &T, float t) {
+    const float ax0 = fmaf(g0.x, T.ix, -T.pox), ax1 = fmaf(g1.x, T.ix, -T.pox);
+    const float ay0 = fmaf(g0.y, T.iy, -T.poy), ay1 = fmaf(g1.y, T.iy, -T.poy);
+    const float az0 = fmaf(g0.z, T.iz, -T.poz), az1 = fmaf(g1.z, T.iz, -T.poz);
+    const float lo = fmaxf(fmaxf(fminf(ax0, ax1), fminf(ay0, ay1)), fmaxf(fminf(az0, az1), T.tmin));
+    const float hi = fminf(fminf(fmaxf(ax0, ax1), fmaxf(ay0, ay1)), fminf(fmaxf(az0, az1), T.tmax));
+    const float m = 1e-5f * fabsf(t) + T.base * fmaxf(fmaxf(fabsf(T.ix), fabsf(T.iy)), fabsf(T.iz));
+    return lo + m < t && t < hi - m;     // false on NaN
+}
 
 template <bool COUNT>
 __device__ __forceinline__ void fast_leaf(const DScene &S, FastTrav &T, const RngKey &key, unsigned &prim_tests) {
@@ -215,12 +242,14 @@ __device__ __forceinline__ void fast_leaf(const DScene &S, FastTrav &T, const Rn
         Rng g;
         rng_init(g, key.seed, key.pixel, key.sample);
         g.bounce = key.bounce;
-        const Ray rr = T.r;      // a copy for the out-of-line call: taking T.r's address would pin the whole state in local memory
-        h = fast_object_leaf<COUNT>(S, rr, T.tmin, T.tmax, &g, obj, code & FAST_LEAF_TWICE, t, pid, prim_tests);
+        // a leaf that is not a bare sphere: a run of primitives (Box, MovingSphere, wrapped objects, media), out of line
+        const int4 o = __ldg(&S.objects[obj]);
+        h = object_hit<COUNT>(S, T.r, T.tmin, T.tmax, &g, o.x, o.y, 0, (code & FAST_LEAF_TWICE) ? 2 : 1, t, pid, prim_tests);
     }
     if (h && (t < T.best || (t == T.best && obj > T.best_obj))) {
         const float4 g0 = __ldg(S.fast_guards + 2 * (size_t)obj), g1 = __ldg(S.fast_guards + 2 * (size_t)obj + 1);
-        if (aabb_hit(g0.x, g0.y, g0.z, g1.x, g1.y, g1.z, T.r, T.tmin, T.tmax)) {   // the reference reaches this leaf
+        if (guard_surely_passes(g0, g1, T, t) ||
+            aabb_hit(g0.x, g0.y, g0.z, g1.x, g1.y, g1.z, T.r, T.tmin, T.tmax)) {   // the reference reaches this leaf
             T.best = t; T.best_obj = obj; T.best_prim = pid;
             T.bestc = fminf(t, T.tmax);
             T.eta = fminf(T.eta_g, fmaf(T.Kd, T.bestc, T.base));

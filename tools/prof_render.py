@@ -44,6 +44,11 @@ def main():
     ms = a.elapsed_time(z) / args.reps
     print(f"{args.scene} kernel={args.kernel} {W}x{H}x{args.spp}: {ms:.2f} ms, {st.paths / ms / 1e3:.1f} Mpaths/s, "
           f"{st.rays / ms / 1e3:.1f} Mrays/s, rays/path {st.rays / max(st.paths, 1):.3f}, launches {st.launches}", flush=True)
+    pr = scene.render_profile()
+    if pr.sampled_iterations:
+        n = pr.sampled_iterations
+        print(f"  wavefront: {pr.iterations} iterations, pool {pr.pool_slots}, extend {pr.extend_ms_sum / n:.3f} ms/it, "
+              f"shade {pr.shade_ms_sum / n:.3f} ms/it (sampled {n})", flush=True)
 
 
 if __name__ == "__main__":
