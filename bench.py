@@ -191,7 +191,7 @@ def run_product(args):
     sptr = stream.cuda_stream
 
     W, H, spp = args.width, args.height, args.spp
-    host = pkg.HostScene(SCENE, seed=SCENE_SEED, wrap=True)
+    host = pkg.HostScene(args.scene, seed=SCENE_SEED, wrap=True)
     scene = pkg.DeviceScene(host.desc, device=local)
     cam = pkg.main_camera(W, H)
     # spp sharding: rank g renders samples [b_g, b_g + n_g); the union is [0, spp) for any world size
@@ -329,7 +329,7 @@ def run_product(args):
     line = {
         "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD if (W, H, spp) == (WIDTH, HEIGHT, SPP) else f"random-spheres scene {W}x{H}, {spp} spp, depth {DEPTH}",
+        "config": {"workload": WORKLOAD if (W, H, spp, args.scene) == (WIDTH, HEIGHT, SPP, SCENE) else f"{args.scene} scene {W}x{H}, {spp} spp, depth {DEPTH}",
                    "scene_seed": SCENE_SEED, "render_seed": RENDER_SEED, "parallelism": f"spp-sharded x{world}, NCCL sum-reduce of fp32 accumulators",
                    "kernel": kernel_name, "traverse": {1: "exact", 2: "fast"}[wc.traverse],
                    "l2": "flushed between timed iterations (256 MiB fill); scene is L2-resident by design"},
@@ -400,6 +400,7 @@ def main():
     ap.add_argument("--width", type=int, default=WIDTH)
     ap.add_argument("--height", type=int, default=HEIGHT)
     ap.add_argument("--spp", type=int, default=SPP)
+    ap.add_argument("--scene", default=SCENE, help="random_ned (configs[1], the default) | cornell_ned | cornell_smoke_ned (configs[3]'s scene)")
     ap.add_argument("--traverse", type=int, default=0, help="0 auto, 1 exact, 2 fast")
     ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 megakernel, 2 wavefront")
     ap.add_argument("--no-bvh", action="store_true", help="skip the config-5 BVH hit-test figures")
@@ -407,6 +408,8 @@ def main():
     ap.add_argument("--bvh-spheres", type=int, default=1000000)
     ap.add_argument("--bvh-skip-exact", action="store_true")
     args = ap.parse_args()
+    if args.scene != SCENE and not args.no_cpu:
+        args.no_cpu = True          # the CPU legs time configs[1]; other scenes are scaling / tuning runs
     if args.impl == "reference":
         run_reference(args)
     else:
