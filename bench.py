@@ -359,7 +359,7 @@ def bvh_hit_bench(pkg, abi, torch, dev_t, stream, args):
     """configs[4]: closest-hit-only harness on N random spheres, coherent + incoherent ray sets."""
     import numpy as np
     ob = pkg.raysets
-    n_spheres, n_side, n_inc = args.bvh_spheres, 2048, 1 << 22
+    n_spheres, n_side, n_inc = args.bvh_spheres, 4096, 1 << 24      # 2^24 rays per class
     t0 = time.perf_counter()
     host = pkg.HostScene("bvh_stress", seed=SCENE_SEED, n=n_spheres)
     t1 = time.perf_counter()
@@ -388,6 +388,15 @@ def bvh_hit_bench(pkg, abi, torch, dev_t, stream, args):
         out[f"{name}_hit_fraction"] = float((hits["prim_id"] >= 0).mean())
         nv, pt = scene.trace_counters(rays[: 1 << 18], traverse=abi.TRAVERSE_FAST)
         out[f"{name}_fast_node_visits_per_ray"], out[f"{name}_fast_prim_tests_per_ray"] = nv, pt
+        # fractions of the FP32-issue roofline: counted work of this traversal, and the BVH-quality-independent
+        # floor of 2*log2(N) slab tests + 1 sphere test = 1104 lane-ops per ray
+        sms, mhz = sm_count_and_clock(torch)
+        peak = sms * 128 * mhz * 1e6
+        rate = out[f"{name}_fast_mrays_per_s"] * 1e6
+        out[f"{name}_fast_counted_ops_per_ray"] = OPS_NODE4 * nv + OPS_PRIM * pt + OPS_HIT * out[f"{name}_hit_fraction"]
+        out[f"{name}_fast_frac_fp32_issue_counted"] = rate * out[f"{name}_fast_counted_ops_per_ray"] / peak
+        out[f"{name}_fast_frac_fp32_issue_floor1104"] = rate * 1104.0 / peak
+    out["rays_per_class"] = {k: int(len(v)) for k, v in sets.items()}
     return out
 
 

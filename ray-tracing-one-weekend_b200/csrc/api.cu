@@ -297,6 +297,11 @@ int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out)
     DScene &D = s->d;
     D.top_kind = desc->top_kind;
     D.root_xf_begin = desc->root_xform_begin; D.root_xf_count = desc->root_xform_count;
+    for (int i = 0; i < 4 && i < desc->root_xform_count; ++i) {
+        const rtow_xform &x = desc->xforms[desc->root_xform_begin + i];
+        float t; std::memcpy(&t, &x.type, 4);
+        D.root_xf[i] = make_float4(t, x.f[0], x.f[1], x.f[2]);
+    }
     D.n_prims = desc->n_prims; D.n_objects = desc->n_objects;
     D.n_prims_top = desc->n_objects ? desc->objects[desc->n_objects - 1].prim_begin + desc->objects[desc->n_objects - 1].prim_count : 0;
     D.has_perlin = desc->perlin ? 1 : 0;

@@ -35,7 +35,7 @@ __global__ void __launch_bounds__(256) trace_kernel(DScene S, const rtow_ray *__
         float tmin = __ldg(q + 7), tmax = __ldg(q + 8);
         Rng g;
         rng_init(g, seed, (uint32_t)i, (uint32_t)(i >> 32));
-        chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, r);
+        root_ray(S, r);
         float t; int pid;
         float4 o0, o1, o2;
         if (closest_hit<COUNT>(S, traverse, r, tmin, tmax, &g, t, pid, nv, pt)) {
@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, c
                     r.time = __ldg(q + 6);
                     const float tmin = __ldg(q + 7), tmax = __ldg(q + 8);
                     key.pixel = (uint32_t)idx; key.sample = (uint32_t)(idx >> 32);
-                    chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, r);
+                    root_ray(S, r);
                     if (fast_covers(S, r, tmin, tmax)) {
                         fast_begin(S, r, tmin, tmax, T);
                     } else {
@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(256) trace_finish_kernel(DScene S, const rtow_
         r.ox = __ldg(q + 0); r.oy = __ldg(q + 1); r.oz = __ldg(q + 2);
         r.dx = __ldg(q + 3); r.dy = __ldg(q + 4); r.dz = __ldg(q + 5);
         r.time = __ldg(q + 6);
-        chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, r);
+        root_ray(S, r);
         const float2 res = *reinterpret_cast<const float2 *>(hits + i);
         float t = res.x; int pid = __float_as_int(res.y);
         if (pid == RTOW_NEEDS_EXACT) {
@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(256) render_mega_kernel(DScene S, rtow_camera 
         g.bounce = (uint32_t)depth;
         rays++;
         Ray rl = r;
-        chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, rl);
+        root_ray(S, rl);
         float t; int pid;
         if (!closest_hit<COUNT>(S, L.traverse, rl, 0.001f, FLT_MAX, &g, t, pid, nv, pt)) {
             if (L.global_illum_en) {

@@ -30,6 +30,7 @@ enum { ENTRY_NODE = -1, ENTRY_OBJECT = 0, ENTRY_SPHERE = 1 };
 struct DScene {
     int32_t top_kind;
     int32_t root_xf_begin, root_xf_count;
+    float4 root_xf[4];            // copy of the root chain when it has <= 4 ops: read from the parameter bank, no load latency
     int32_t n_entries;
     int32_t n_prims_top;          // LIST mode: the root run is prims[0, n_prims_top)
     int32_t n_prims, n_objects;
@@ -127,6 +128,28 @@ __device__ __forceinline__ void chain_ray(const float4 *__restrict__ xf, int beg
         }
     }
 }
+// the root aggregate's own wrappers (main.cpp:132,136 put the world behind one Translate)
+__device__ __forceinline__ void root_ray(const DScene &S, Ray &r) {
+    if (S.root_xf_count <= 4) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (i < S.root_xf_count) {
+                const float4 x = S.root_xf[i];
+                const int type = __float_as_int(x.x);
+                if (type == RTOW_XF_TRANSLATE) {
+                    r.ox = r.ox - x.y; r.oy = r.oy - x.z; r.oz = r.oz - x.w;
+                } else if (type == RTOW_XF_ROTATE_Y) {
+                    float s = x.y, c = x.z;
+                    float ox = c * r.ox - s * r.oz, oz = s * r.ox + c * r.oz;
+                    float dx = c * r.dx - s * r.dz, dz = s * r.dx + c * r.dz;
+                    r.ox = ox; r.oz = oz; r.dx = dx; r.dz = dz;
+                }
+            }
+        }
+    } else {
+        chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, r);
+    }
+}
 __device__ __forceinline__ void chain_hit(const float4 *__restrict__ xf, int begin, int n, float p[3], float nrm[3]) {
     for (int i = n - 1; i >= 0; --i) {
         float4 x = __ldg(&xf[begin + i]);
@@ -141,6 +164,29 @@ __device__ __forceinline__ void chain_hit(const float4 *__restrict__ xf, int beg
         } else {
             nrm[0] = -nrm[0]; nrm[1] = -nrm[1]; nrm[2] = -nrm[2];
         }
+    }
+}
+__device__ __forceinline__ void root_hit(const DScene &S, float p[3], float nrm[3]) {
+    if (S.root_xf_count <= 4) {
+#pragma unroll
+        for (int i = 3; i >= 0; --i) {
+            if (i < S.root_xf_count) {
+                const float4 x = S.root_xf[i];
+                const int type = __float_as_int(x.x);
+                if (type == RTOW_XF_TRANSLATE) {
+                    p[0] += x.y; p[1] += x.z; p[2] += x.w;
+                } else if (type == RTOW_XF_ROTATE_Y) {
+                    float s = x.y, c = x.z;
+                    float px = c * p[0] + s * p[2], pz = -s * p[0] + c * p[2];
+                    float nx = c * nrm[0] + s * nrm[2], nz = -s * nrm[0] + c * nrm[2];
+                    p[0] = px; p[2] = pz; nrm[0] = nx; nrm[2] = nz;
+                } else {
+                    nrm[0] = -nrm[0]; nrm[1] = -nrm[1]; nrm[2] = -nrm[2];
+                }
+            }
+        }
+    } else {
+        chain_hit(S.xforms, S.root_xf_begin, S.root_xf_count, p, nrm);
     }
 }
 
@@ -405,7 +451,7 @@ __device__ __forceinline__ void prim_record(const DScene &S, int pid, const Ray 
         v = (y - f0.z) / (f0.w - f0.z);
     }
     chain_hit(S.xforms, p.xf_begin, p.xf_count, pt, n);
-    chain_hit(S.xforms, S.root_xf_begin, S.root_xf_count, pt, n);
+    root_hit(S, pt, n);
     h.t = t; h.prim = pid; h.mat = p.mat_id; h.u = u; h.v = v;
     h.p[0] = pt[0]; h.p[1] = pt[1]; h.p[2] = pt[2];
     h.n[0] = n[0]; h.n[1] = n[1]; h.n[2] = n[2];

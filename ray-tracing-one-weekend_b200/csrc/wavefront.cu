@@ -157,13 +157,13 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
                 const unsigned long long mine = base + __popc(need & ((1u << lane) - 1u));
                 if (mine < (unsigned long long)W.pool) {
                     const int4 id = W.ids[mine];
+                    const float4 a = W.rayA[mine], b = W.rayB[mine];      // with the ids, not after them: one load latency, not two
                     if (id.w >= 0) {
                         slot = (int)mine; has_ray = true; rays++;
-                        const float4 a = W.rayA[slot], b = W.rayB[slot];
                         Ray r;
                         r.ox = a.x; r.oy = a.y; r.oz = a.z; r.time = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z;
                         key.pixel = (uint32_t)id.x; key.sample = (uint32_t)id.y; key.bounce = (uint32_t)id.w;
-                        chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, r);
+                        root_ray(S, r);
                         if (use_fast && fast_covers(S, r, 0.001f, FLT_MAX)) {
                             fast_begin(S, r, 0.001f, FLT_MAX, T);
                         } else {
@@ -268,7 +268,7 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DScene S, WavefrontLaunch
             ended = true;
         } else {
             Ray rl = r;
-            chain_ray(S.xforms, S.root_xf_begin, S.root_xf_count, rl);
+            root_ray(S, rl);
             MatRec m = load_material(S, __ldg(&S.prims[pid * 5]).y);
             Hit h;
             prim_record(S, pid, rl, hr.x, m.needs_uv != 0, h);
