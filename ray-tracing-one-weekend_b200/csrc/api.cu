@@ -208,10 +208,9 @@ int ensure_wavefront(rtow_scene *s, int pool, size_t pixels) {
     pool = std::max(pool, s->wf_pool); pixels = std::max(pixels, s->wf_pixels);
     auto grab = [&](void **p, size_t bytes) { cudaError_t e = cudaMalloc(p, bytes); if (e == cudaSuccess) s->wf_allocs.push_back(*p); return e; };
     WavefrontLaunch &W = s->wf;
-    CUDA_TRY(grab((void **)&W.rayA, (size_t)pool * 16)); CUDA_TRY(grab((void **)&W.rayB, (size_t)pool * 16));
-    CUDA_TRY(grab((void **)&W.hit, (size_t)pool * 8));
-    CUDA_TRY(grab((void **)&W.thr, (size_t)pool * 16)); CUDA_TRY(grab((void **)&W.rad, (size_t)pool * 16));
-    CUDA_TRY(grab((void **)&W.ids, (size_t)pool * 16));
+    CUDA_TRY(grab((void **)&W.ray, (size_t)pool * 32));
+    CUDA_TRY(grab((void **)&W.tl, (size_t)pool * 32));
+    CUDA_TRY(grab((void **)&W.idh, (size_t)pool * 32));
     CUDA_TRY(grab((void **)&W.queue, (size_t)pool * RTOW_WF_MAX_CLASSES * 4));
     CUDA_TRY(grab((void **)&W.counts, 2 * RTOW_WF_MAX_CLASSES * 4));
     CUDA_TRY(grab((void **)&W.fixed, pixels * 3 * 8));

@@ -34,10 +34,12 @@ struct WavefrontLaunch {
     int pool;                             // path slots (multiple of 256)
     unsigned long long total_items;       // work items = pixel groups of 32 x samples (incl. padding pixels)
     // per-slot state (SoA in HBM)
-    float4 *rayA, *rayB;                  // {o.xyz, time} {d.xyz, -}
-    float2 *hit;                          // {t, prim id bits} (prim < 0: miss)
-    float4 *thr, *rad;                    // path throughput T, radiance so far L
-    int4 *ids;                            // {pixel, sample, next Philox draw, depth}; depth < 0: the slot is dead
+    // three arrays of 32-byte elements (two 16-byte halves each), so that the shade kernel -- which reaches its slot
+    // through a queue, one scattered line per lane -- moves a slot with three 256-bit loads and stores instead of six
+    float4 *ray;                          // [2*slot] {o.xyz, time}  [2*slot+1] {d.xyz, -}
+    float4 *tl;                           // [2*slot] path throughput T  [2*slot+1] radiance so far L
+    int4 *idh;                            // [2*slot] {pixel, sample, next Philox draw, depth}; depth < 0: the slot is dead
+                                          // [2*slot+1] {t bits, prim id (< 0: miss), -, -} written by the extend kernel
     int *queue;                           // RTOW_WF_MAX_CLASSES x pool slot indices, by shading class
     unsigned *counts;                     // 2 x RTOW_WF_MAX_CLASSES queue lengths (double-buffered by bounce parity)
     unsigned long long *fixed;            // W*H*3 radiance sums, Q31.32

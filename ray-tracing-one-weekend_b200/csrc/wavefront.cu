@@ -26,6 +26,17 @@ namespace rtow {
 
 #define WF_FIXED_SCALE 4294967296.0   // 2^32: radiance sums in Q31.32
 
+// 256-bit global accesses (LDG.E.256 / STG.E.256); p must be 32-byte aligned
+__device__ __forceinline__ void ld256(const void *p, float4 &a, float4 &b) {
+    asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p) : "memory");
+}
+__device__ __forceinline__ void st256(void *p, const float4 &a, const float4 &b) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 :: "l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w) : "memory");
+}
+
 #define WF_SAMPLE_BLOCK 64
 __device__ __forceinline__ void wf_item_to_pixel(const WavefrontLaunch &W, unsigned long long item, int &pixel, int &sample) {
     // Order of the work items: blocks of WF_SAMPLE_BLOCK sample indices; inside a block, groups of 32 neighbouring
@@ -66,11 +77,9 @@ __device__ __forceinline__ bool wf_start_path(const WavefrontLaunch &W, const rt
     float v = (float)((double)row + (double)jv) / (float)W.L.height;
     Ray r;
     camera_ray(cam, u, v, g, r);
-    W.rayA[slot] = make_float4(r.ox, r.oy, r.oz, r.time);
-    W.rayB[slot] = make_float4(r.dx, r.dy, r.dz, 0.f);
-    W.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
-    W.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
-    W.ids[slot] = make_int4(pixel, W.L.sample_begin + s, (int)g.next, 0);
+    st256(W.ray + 2 * (size_t)slot, make_float4(r.ox, r.oy, r.oz, r.time), make_float4(r.dx, r.dy, r.dz, 0.f));
+    st256(W.tl + 2 * (size_t)slot, make_float4(1.f, 1.f, 1.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f));
+    W.idh[2 * (size_t)slot] = make_int4(pixel, W.L.sample_begin + s, (int)g.next, 0);
     return true;
 }
 
@@ -93,7 +102,7 @@ __device__ __forceinline__ void wf_refill(const WavefrontLaunch &W, const rtow_c
         }
     }
     const unsigned dm = __ballot_sync(full, dead);
-    if (dead) W.ids[slot].w = -1;
+    if (dead) W.idh[2 * (size_t)slot].w = -1;
     if (lane == 0 && dm) atomicAdd(W.dead_slots, (unsigned long long)__popc(dm));
 }
 
@@ -132,7 +141,7 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
                 if (fin) {
                     float t = 0.f; int pid = -1;
                     if (!fast_result(S, T, t, pid)) pid = -1;
-                    W.hit[slot] = make_float2(t, __int_as_float(pid));
+                    *reinterpret_cast<float2 *>(W.idh + 2 * (size_t)slot + 1) = make_float2(t, __int_as_float(pid));
                     cls = pid >= 0 ? __ldg(&S.materials[2 * __ldg(&S.prims[pid * 5]).y + 1]).w : 0;
                     has_ray = false;
                 }
@@ -156,8 +165,9 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
             if (!has_ray) {
                 const unsigned long long mine = base + __popc(need & ((1u << lane) - 1u));
                 if (mine < (unsigned long long)W.pool) {
-                    const int4 id = W.ids[mine];
-                    const float4 a = W.rayA[mine], b = W.rayB[mine];      // with the ids, not after them: one load latency, not two
+                    const int4 id = W.idh[2 * mine];
+                    float4 a, b;
+                    ld256(W.ray + 2 * mine, a, b);        // with the ids, not after them: one load latency, not two
                     if (id.w >= 0) {
                         slot = (int)mine; has_ray = true; rays++;
                         Ray r;
@@ -238,10 +248,12 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DScene S, WavefrontLaunch
     int pixel = 0;
     float Lr[3] = {0.f, 0.f, 0.f};
     if (valid) {
-        const int4 id = W.ids[slot];
-        const float4 a = W.rayA[slot], b = W.rayB[slot];
-        const float2 hr = W.hit[slot];
-        const float4 t4 = W.thr[slot], l4 = W.rad[slot];
+        float4 a, b, t4, l4, idf, hf;
+        ld256(W.ray + 2 * (size_t)slot, a, b);
+        ld256(W.tl + 2 * (size_t)slot, t4, l4);
+        ld256(W.idh + 2 * (size_t)slot, idf, hf);
+        const int4 id = make_int4(__float_as_int(idf.x), __float_as_int(idf.y), __float_as_int(idf.z), __float_as_int(idf.w));
+        const float2 hr = make_float2(hf.x, hf.y);
         float T[3] = {t4.x, t4.y, t4.z};
         Lr[0] = l4.x; Lr[1] = l4.y; Lr[2] = l4.z;
         pixel = id.x;
@@ -280,11 +292,9 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DScene S, WavefrontLaunch
                 Lr[0] += T[0] * em[0]; Lr[1] += T[1] * em[1]; Lr[2] += T[2] * em[2];
                 if (go) {
                     T[0] *= atten[0]; T[1] *= atten[1]; T[2] *= atten[2];
-                    W.rayA[slot] = make_float4(h.p[0], h.p[1], h.p[2], stime);
-                    W.rayB[slot] = make_float4(sd[0], sd[1], sd[2], 0.f);
-                    W.thr[slot] = make_float4(T[0], T[1], T[2], 0.f);
-                    W.rad[slot] = make_float4(Lr[0], Lr[1], Lr[2], 0.f);
-                    W.ids[slot] = make_int4(id.x, id.y, (int)g.next, depth + 1);
+                    st256(W.ray + 2 * (size_t)slot, make_float4(h.p[0], h.p[1], h.p[2], stime), make_float4(sd[0], sd[1], sd[2], 0.f));
+                    st256(W.tl + 2 * (size_t)slot, make_float4(T[0], T[1], T[2], 0.f), make_float4(Lr[0], Lr[1], Lr[2], 0.f));
+                    W.idh[2 * (size_t)slot] = make_int4(id.x, id.y, (int)g.next, depth + 1);
                 } else {
                     ended = true;
                 }

@@ -52,14 +52,15 @@ def test_depth_limit_and_no_global_illum(gpu, abi, port, kernel):
         assert np.abs(img - want["sum"] / np.float32(4)).max() <= 2e-4 * max(1.0, float(want["sum"].max()) / 4)
 
 
-def test_wavefront_equals_megakernel(gpu, abi):
+@pytest.mark.parametrize("W,H,spp", [(160, 90, 32), (37, 23, 70), (64, 36, 129)], ids=["160x90x32", "37x23x70", "64x36x129"])
+def test_wavefront_equals_megakernel(gpu, abi, W, H, spp):
     """Same Philox streams, same path arithmetic: the two kernels differ only in the order of the per-pixel sum
     (fp32 shuffles vs 64-bit fixed point), and the wavefront image is deterministic although slots are handed out
-    dynamically.  A pool smaller than the work (forced regeneration) must not change the image."""
-    import os
+    dynamically.  The sizes cover the work-item order of the wavefront path: a partial 64-sample block only, full blocks
+    plus a partial one, a pixel count that is not a multiple of 32 (padding items).  (Slot regeneration -- more items than pool slots -- is
+    exercised by test_converged_image_matches_reference_golden.)"""
     host = gpu.HostScene("random_ned", seed=12345, image=earth_image())
     dev = gpu.DeviceScene(host.desc)
-    W, H, spp = 160, 90, 32
     cam = gpu.main_camera(W, H)
     a, sa = dev.render(cam, abi.default_render_params(W, H, spp, seed=4, kernel=abi.KERNEL_MEGA))
     b, sb = dev.render(cam, abi.default_render_params(W, H, spp, seed=4, kernel=abi.KERNEL_WAVEFRONT))
