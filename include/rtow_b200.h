@@ -257,6 +257,13 @@ int rtow_render(rtow_scene *scene, const rtow_camera *cam, const rtow_render_par
  * Counters are read with rtow_stream_stats. */
 int rtow_render_accumulate_device(rtow_scene *scene, const rtow_camera *cam,
                                   const rtow_render_params *params, float *d_accum, void *stream);
+
+/* The same, plus the sum of SQUARED per-sample radiance into d_accum_sq (W*H*3 floats, added to; null = not wanted):
+ * with the sample count this is the per-pixel variance image, kept across calls for progressive rendering and
+ * checkpoint / resume (the reference re-renders from scratch, main.cpp:247).  Wavefront kernels
+ * only: RTOW_KERNEL_MEGA with a non-null d_accum_sq returns RTOW_ERR_UNSUPPORTED. */
+int rtow_render_accumulate_moments_device(rtow_scene *scene, const rtow_camera *cam, const rtow_render_params *params,
+                                          float *d_accum, float *d_accum_sq, void *stream);
 /* Blocks until `stream` is idle and returns the counters of the last accumulate call. */
 int rtow_stream_stats(rtow_scene *scene, void *stream, rtow_stats *stats);
 

@@ -38,6 +38,13 @@ int rtow_host_camera(const float look_from[3], const float look_at[3], const flo
  * rgb = W*H*3 linear floats, row 0 = top.  PPM applies the reference tone curve main.cpp:955-970. */
 int rtow_write_ppm(const char *path, const float *rgb_linear, int32_t width, int32_t height);
 int rtow_write_pfm(const char *path, const float *rgb_linear, int32_t width, int32_t height);
+/* OpenEXR 2 scanline file, uncompressed, FLOAT channels B,G,R (hand-rolled writer). */
+int rtow_write_exr(const char *path, const float *rgb_linear, int32_t width, int32_t height);
+
+/* Camera::setLookFromPoint + Camera::setOrientationMatrix (camera.h:166-229; the per-frame update of the
+ * reference's fly-camera, main.cpp:485-642).  orientation = 4x4 row-major, rows 0,1,2 = w,u,v. */
+int rtow_host_camera_oriented(const float look_from[3], const float orientation[16], float vfov, float aspect,
+                              float aperture, float focus_distance, float t0, float t1, rtow_camera *out);
 
 #ifdef __cplusplus
 }

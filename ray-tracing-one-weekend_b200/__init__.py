@@ -11,6 +11,7 @@ loaded under the module name ``rtow_b200`` by ``__graft_entry__.load_package()``
 from . import _abi as abi  # noqa: F401
 from . import raysets  # noqa: F401
 from . import sharding  # noqa: F401
+from .progressive import ProgressiveRender  # noqa: F401
 from .binding import (  # noqa: F401
     RtowError,
     lib,
@@ -21,7 +22,9 @@ from .binding import (  # noqa: F401
     main_camera,
     write_ppm,
     write_pfm,
+    write_exr,
+    oriented_camera,
 )
 
 __all__ = ["abi", "RtowError", "lib", "lib_path", "HostScene", "DeviceScene", "make_camera", "main_camera",
-           "write_ppm", "write_pfm"]
+           "write_ppm", "write_pfm", "write_exr", "oriented_camera", "ProgressiveRender"]

@@ -47,6 +47,7 @@ def lib():
         "rtow_trace_rays_device": (C.c_int, [vp, vp, u64, vp, C.c_int, u64, vp]),
         "rtow_render": (C.c_int, [vp, P(abi.Camera), P(abi.RenderParams), vp, vp, P(abi.Stats)]),
         "rtow_render_accumulate_device": (C.c_int, [vp, P(abi.Camera), P(abi.RenderParams), vp, vp]),
+        "rtow_render_accumulate_moments_device": (C.c_int, [vp, P(abi.Camera), P(abi.RenderParams), vp, vp, vp]),
         "rtow_stream_stats": (C.c_int, [vp, vp, P(abi.Stats)]),
         "rtow_resolve_device": (C.c_int, [vp, vp, i32, i32, i32, vp, vp, vp]),
         "rtow_trace_counters": (C.c_int, [vp, vp, u64, C.c_int, P(C.c_double), P(C.c_double)]),
@@ -61,6 +62,8 @@ def lib():
         "rtow_host_camera": (C.c_int, [P(f32 * 3), P(f32 * 3), P(f32 * 3), f32, f32, f32, f32, f32, f32, P(abi.Camera)]),
         "rtow_write_ppm": (C.c_int, [C.c_char_p, vp, i32, i32]),
         "rtow_write_pfm": (C.c_int, [C.c_char_p, vp, i32, i32]),
+        "rtow_write_exr": (C.c_int, [C.c_char_p, vp, i32, i32]),
+        "rtow_host_camera_oriented": (C.c_int, [P(f32 * 3), P(f32 * 16), f32, f32, f32, f32, f32, f32, P(abi.Camera)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)   # AttributeError here = the library does not export what the header declares
@@ -71,9 +74,9 @@ def lib():
 
 EXPORTED_SYMBOLS = [
     "rtow_device_count", "rtow_scene_create", "rtow_scene_destroy", "rtow_trace_rays", "rtow_trace_rays_device",
-    "rtow_render", "rtow_render_accumulate_device", "rtow_stream_stats", "rtow_resolve_device", "rtow_trace_counters", "rtow_render_counters", "rtow_render_profile",
+    "rtow_render", "rtow_render_accumulate_device", "rtow_render_accumulate_moments_device", "rtow_stream_stats", "rtow_resolve_device", "rtow_trace_counters", "rtow_render_counters", "rtow_render_profile",
     "rtow_last_error", "rtow_build_info", "rtow_host_scene_build", "rtow_host_scene_desc", "rtow_host_scene_free",
-    "rtow_host_set_image", "rtow_host_camera", "rtow_write_ppm", "rtow_write_pfm",
+    "rtow_host_set_image", "rtow_host_camera", "rtow_write_ppm", "rtow_write_pfm", "rtow_write_exr", "rtow_host_camera_oriented",
 ]
 
 
@@ -91,6 +94,15 @@ def make_camera(look_from, look_at, up, vfov, aspect, aperture, focus, t0=0.0, t
     cam = abi.Camera()
     _check(lib().rtow_host_camera(C.byref(_vec3(look_from)), C.byref(_vec3(look_at)), C.byref(_vec3(up)),
                                   vfov, aspect, aperture, focus, t0, t1, C.byref(cam)))
+    return cam
+
+
+def oriented_camera(look_from, orientation, vfov, aspect, aperture=2.0, focus=1000.0, t0=0.0, t1=1.0):
+    """Camera::setLookFromPoint + setOrientationMatrix (camera.h:166-229): the reference's per-frame fly-camera update.
+    orientation: 4x4, rows 0,1,2 = w,u,v."""
+    cam = abi.Camera()
+    m = (C.c_float * 16)(*[float(x) for x in np.asarray(orientation, dtype=np.float32).reshape(16)])
+    _check(lib().rtow_host_camera_oriented(C.byref(_vec3(look_from)), C.byref(m), vfov, aspect, aperture, focus, t0, t1, C.byref(cam)))
     return cam
 
 
@@ -204,6 +216,9 @@ class DeviceScene:
     def accumulate_device(self, cam, params, d_accum_ptr, stream=None):
         _check(lib().rtow_render_accumulate_device(self._h, C.byref(cam), C.byref(params), d_accum_ptr, stream))
 
+    def accumulate_moments_device(self, cam, params, d_accum_ptr, d_accum_sq_ptr, stream=None):
+        _check(lib().rtow_render_accumulate_moments_device(self._h, C.byref(cam), C.byref(params), d_accum_ptr, d_accum_sq_ptr, stream))
+
     def stream_stats(self, stream=None):
         st = abi.Stats()
         _check(lib().rtow_stream_stats(self._h, stream, C.byref(st)))
@@ -221,3 +236,8 @@ def write_ppm(path, rgb):
 def write_pfm(path, rgb):
     rgb = np.ascontiguousarray(rgb, dtype=np.float32)
     _check(lib().rtow_write_pfm(str(path).encode(), rgb.ctypes.data, rgb.shape[1], rgb.shape[0]))
+
+
+def write_exr(path, rgb):
+    rgb = np.ascontiguousarray(rgb, dtype=np.float32)
+    _check(lib().rtow_write_exr(str(path).encode(), rgb.ctypes.data, rgb.shape[1], rgb.shape[0]))

@@ -34,6 +34,7 @@ struct rtow_scene {
     WavefrontLaunch wf;
     int wf_pool = 0; size_t wf_pixels = 0;
     std::vector<void *> wf_allocs;
+    unsigned long long *wf_sq = nullptr; size_t wf_sq_pixels = 0;   // Q43.20 sums of squares (rtow_render_accumulate_moments_device)
     unsigned long long *h_pinned = nullptr;
     bool pending_wavefront = false; uint64_t pending_paths = 0;
     WavefrontProfile wf_prof;
@@ -273,6 +274,7 @@ void rtow_scene_destroy(rtow_scene *s) {
     for (void *p : {(void *)s->d_counters, s->d_rays, s->d_hits, (void *)s->d_accum, (void *)s->d_rgb, (void *)s->d_bgra})
         if (p) cudaFree(p);
     for (void *p : s->wf_allocs) cudaFree(p);
+    if (s->wf_sq) cudaFree(s->wf_sq);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -494,6 +496,11 @@ int rtow_trace_counters(rtow_scene *s, const rtow_ray *rays, uint64_t n, int tra
 }
 
 int rtow_render_accumulate_device(rtow_scene *s, const rtow_camera *cam, const rtow_render_params *params, float *d_accum, void *stream) {
+    return rtow_render_accumulate_moments_device(s, cam, params, d_accum, nullptr, stream);
+}
+
+int rtow_render_accumulate_moments_device(rtow_scene *s, const rtow_camera *cam, const rtow_render_params *params, float *d_accum,
+                                          float *d_accum_sq, void *stream) {
     RenderLaunch L;
     if (int rc = check_render_args(s, cam, params, &L)) return rc;
     if (!d_accum) return set_error(RTOW_ERR_INVALID_ARG, "rtow_render_accumulate_device: null accumulator");
@@ -502,7 +509,11 @@ int rtow_render_accumulate_device(rtow_scene *s, const rtow_camera *cam, const r
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTOW_N_COUNTERS * sizeof(unsigned long long), st));
     CUDA_TRY(cudaEventRecord(s->ev0, st));
     static const int auto_kernel = [] { const char *e = getenv("RTOW_KERNEL"); return e ? atoi(e) : RTOW_KERNEL_WAVEFRONT; }();   // measured on B200: wavefront beats the megakernel 1.6x-4.5x on every scene
-    const int kernel = params->kernel == RTOW_KERNEL_AUTO ? auto_kernel : params->kernel;
+    int kernel = params->kernel == RTOW_KERNEL_AUTO ? auto_kernel : params->kernel;
+    if (d_accum_sq) {
+        if (params->kernel == RTOW_KERNEL_MEGA) return set_error(RTOW_ERR_UNSUPPORTED, "second moments are produced by the wavefront kernels only");
+        kernel = RTOW_KERNEL_WAVEFRONT;
+    }
     if (kernel == RTOW_KERNEL_WAVEFRONT) {
         // Synchronises `stream` internally (the host loop polls the pool for completion).
         static const long long pool_cap = [] { const char *e = getenv("RTOW_WF_POOL"); return e ? atoll(e) : (1ll << 20); }();
@@ -511,9 +522,16 @@ int rtow_render_accumulate_device(rtow_scene *s, const rtow_camera *cam, const r
         long long pool = (long long)std::min<unsigned long long>(items, (unsigned long long)pool_cap);
         pool = (pool + 255) / 256 * 256;
         if (int rc = ensure_wavefront(s, (int)pool, (size_t)n_pixels)) return rc;
+        if (d_accum_sq && (!s->wf_sq || s->wf_sq_pixels < (size_t)n_pixels)) {
+            if (s->wf_sq) cudaFree(s->wf_sq);
+            s->wf_sq = nullptr; s->wf_sq_pixels = 0;
+            CUDA_TRY(cudaMalloc((void **)&s->wf_sq, (size_t)n_pixels * 3 * 8));
+            s->wf_sq_pixels = (size_t)n_pixels;
+        }
         s->wf.L = L; s->wf.pool = (int)pool; s->wf.total_items = items;
+        s->wf.fixed_sq = d_accum_sq ? s->wf_sq : nullptr;
         uint32_t launches = 0;
-        CUDA_TRY(run_wavefront(s->d, *cam, s->wf, d_accum, s->h_pinned, st, &launches, &s->wf_prof));
+        CUDA_TRY(run_wavefront(s->d, *cam, s->wf, d_accum, d_accum_sq, s->h_pinned, st, &launches, &s->wf_prof));
         CUDA_TRY(cudaMemcpyAsync(s->d_counters, s->wf.stats, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st));
         s->pending_launches = launches;
         s->pending_wavefront = true;

@@ -115,4 +115,62 @@ int rtow_write_pfm(const char *path, const float *rgb, int32_t W, int32_t H) {
     return RTOW_OK;
 }
 
+// OpenEXR 2, single-part scanline, no compression, three FLOAT channels (stored B, G, R: channel lists are alphabetical).
+// Hand-rolled (no OpenEXR library in this image); readable by any EXR loader.  SURVEY 8(f) rank 2.
+int rtow_write_exr(const char *path, const float *rgb, int32_t W, int32_t H) {
+    if (!path || !rgb || W <= 0 || H <= 0) return rtow::set_error(RTOW_ERR_INVALID_ARG, "rtow_write_exr: bad argument");
+    std::vector<uint8_t> hdr;
+    auto put = [&](const void *p, size_t n) { const uint8_t *b = (const uint8_t *)p; hdr.insert(hdr.end(), b, b + n); };
+    auto put_i32 = [&](int32_t v) { put(&v, 4); };           // little-endian host (x86-64 / aarch64 as built here)
+    auto put_f32 = [&](float v) { put(&v, 4); };
+    auto put_str = [&](const char *z) { put(z, std::strlen(z) + 1); };
+    auto attr = [&](const char *name, const char *type, int32_t size) { put_str(name); put_str(type); put_i32(size); };
+    put_i32(20000630); put_i32(2);
+    attr("channels", "chlist", 3 * (2 + 16) + 1);
+    for (const char *c : {"B", "G", "R"}) { put_str(c); put_i32(2 /*FLOAT*/); put_i32(0 /*pLinear + reserved*/); put_i32(1); put_i32(1); }
+    hdr.push_back(0);
+    attr("compression", "compression", 1); hdr.push_back(0);
+    attr("dataWindow", "box2i", 16); put_i32(0); put_i32(0); put_i32(W - 1); put_i32(H - 1);
+    attr("displayWindow", "box2i", 16); put_i32(0); put_i32(0); put_i32(W - 1); put_i32(H - 1);
+    attr("lineOrder", "lineOrder", 1); hdr.push_back(0);      // increasing y: row 0 = top, like our buffers
+    attr("pixelAspectRatio", "float", 4); put_f32(1.0f);
+    attr("screenWindowCenter", "v2f", 8); put_f32(0.0f); put_f32(0.0f);
+    attr("screenWindowWidth", "float", 4); put_f32(1.0f);
+    hdr.push_back(0);
+    FILE *f = std::fopen(path, "wb");
+    if (!f) return rtow::set_error(RTOW_ERR_IO, std::string("cannot open ") + path);
+    std::fwrite(hdr.data(), 1, hdr.size(), f);
+    const uint64_t row_bytes = (uint64_t)W * 3 * 4, block = 8 + row_bytes;
+    uint64_t off = hdr.size() + (uint64_t)H * 8;
+    for (int y = 0; y < H; ++y, off += block) std::fwrite(&off, 8, 1, f);
+    std::vector<float> row((size_t)W * 3);
+    for (int32_t y = 0; y < H; ++y) {
+        const float *src = rgb + (size_t)y * W * 3;
+        for (int x = 0; x < W; ++x) { row[x] = src[3 * x + 2]; row[(size_t)W + x] = src[3 * x + 1]; row[2 * (size_t)W + x] = src[3 * x]; }
+        int32_t size = (int32_t)row_bytes;
+        std::fwrite(&y, 4, 1, f); std::fwrite(&size, 4, 1, f);
+        std::fwrite(row.data(), 4, row.size(), f);
+    }
+    bool ok = std::ferror(f) == 0;
+    std::fclose(f);
+    return ok ? RTOW_OK : rtow::set_error(RTOW_ERR_IO, std::string("write failed: ") + path);
+}
+
+// Camera::setLookFromPoint + Camera::setOrientationMatrix (camera.h:166-229): what the reference's fly-camera does every
+// frame (main.cpp:485-642, host-only).  `orientation` = the 4x4 matrix row-major; rows 0,1,2 are w,u,v (camera.h:328-332).
+// A moved camera needs a fresh POD only: the scene stays on the device.
+int rtow_host_camera_oriented(const float look_from[3], const float orientation[16], float vfov, float aspect, float aperture,
+                              float focus_distance, float t0, float t1, rtow_camera *out) {
+    using rtow::api::vec3;
+    if (!look_from || !orientation || !out) return rtow::set_error(RTOW_ERR_INVALID_ARG, "rtow_host_camera_oriented: null argument");
+    rtow::api::Camera cam(vec3(look_from[0], look_from[1], look_from[2]), vec3(1, 0, 0), vec3(0, 0, -1), vfov, aspect, aperture,
+                          focus_distance, t0, t1);
+    rtow::api::mat4x4 m;
+    for (int r = 0; r < 4; ++r) m.m[r] = rtow::api::vec4(orientation[4 * r], orientation[4 * r + 1], orientation[4 * r + 2], orientation[4 * r + 3]);
+    cam.setLookFromPoint(vec3(look_from[0], look_from[1], look_from[2]));
+    cam.setOrientationMatrix(m);
+    *out = rtow::camera_pod<rtow::api::Traits>(cam, false);
+    return RTOW_OK;
+}
+
 }  // extern "C"

@@ -43,6 +43,7 @@ struct WavefrontLaunch {
     int *queue;                           // RTOW_WF_MAX_CLASSES x pool slot indices, by shading class
     unsigned *counts;                     // 2 x RTOW_WF_MAX_CLASSES queue lengths (double-buffered by bounce parity)
     unsigned long long *fixed;            // W*H*3 radiance sums, Q31.32
+    unsigned long long *fixed_sq;         // W*H*3 sums of squared per-sample radiance, Q43.20; null unless moments were asked for
     unsigned long long *control;          // [0] next work item [1] dead slots [2] extend queue head [3] rays traced
     unsigned long long *next_item, *dead_slots, *extend_head, *stats;
 };
@@ -51,7 +52,7 @@ struct WavefrontProfile {
     float extend_ms = 0.f, shade_ms = 0.f;
     uint32_t samples = 0, iterations = 0, pool = 0;
 };
-cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaunch &W, float *d_accum, unsigned long long *h_pinned,
+cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaunch &W, float *d_accum, float *d_accum_sq, unsigned long long *h_pinned,
                           cudaStream_t stream, uint32_t *launches_out, WavefrontProfile *prof);
 
 void launch_resolve(const float *d_accum, int width, int height, int spp, float *d_rgb, uint8_t *d_bgra, cudaStream_t stream);

@@ -1,10 +1,10 @@
 // rtow_cli.cpp -- headless front end: replaces the reference's Win32 shell (main.cpp:69-787: window, message pump,
 // worker threads, 10 000-frame loop) and winDIBbitmap.cpp's BMP dump.  Builds a scene through the scene API, renders it
 // through the C ABI on one GPU and writes the frame as PPM (8-bit, reference tone curve main.cpp:955-970) and PFM
-// (linear float), plus one JSON line of statistics.  Uses only include/rtow_b200.h + rtow_b200_scenes.h.
+// (linear float; --exr adds an uncompressed OpenEXR), plus one JSON line of statistics.  Uses only include/rtow_b200.h + rtow_b200_scenes.h.
 //
 //   rtow_cli --scene random_ned --width 1920 --height 1080 --spp 64 --out frame [--seed 1] [--scene-seed 12345]
-//            [--depth 50] [--kernel 0|1|2] [--traverse 0|1|2] [--device 0] [--n 1000000 (bvh_stress)] [--no-wrap]
+//            [--depth 50] [--kernel 0|1|2] [--traverse 0|1|2] [--device 0] [--n 1000000 (bvh_stress)] [--no-wrap] [--exr]
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -21,7 +21,7 @@ static int fail(const char *what) {
 
 int main(int argc, char **argv) {
     std::string scene = "cornell_ned", out = "frame";   // main() renders cornellBox_NED by default (main.cpp:136)
-    int W = 800, H = 800, spp = 64, depth = 50, kernel = 0, traverse = 0, device = 0, n = 0, wrap = 1;   // defines.h:7-9,27
+    int W = 800, H = 800, spp = 64, depth = 50, kernel = 0, traverse = 0, device = 0, n = 0, wrap = 1, exr = 0;   // defines.h:7-9,27
     unsigned long long seed = 1, scene_seed = 12345;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
@@ -39,6 +39,7 @@ int main(int argc, char **argv) {
         else if (a == "--seed") seed = std::strtoull(val(), nullptr, 10);
         else if (a == "--scene-seed") scene_seed = std::strtoull(val(), nullptr, 10);
         else if (a == "--no-wrap") wrap = 0;
+        else if (a == "--exr") exr = 1;
         else { std::fprintf(stderr, "rtow_cli: unknown option %s\n", a.c_str()); return 2; }
     }
     if (rtow_device_count() < 1) { std::fprintf(stderr, "rtow_cli: no CUDA device (this library has no CPU path)\n"); return 3; }
@@ -64,6 +65,7 @@ int main(int argc, char **argv) {
     if (rtow_render(dev, &cam, &p, rgb.data(), bgra.data(), &st) != RTOW_OK) return fail("render");
     if (rtow_write_ppm((out + ".ppm").c_str(), rgb.data(), W, H) != RTOW_OK) return fail("write ppm");
     if (rtow_write_pfm((out + ".pfm").c_str(), rgb.data(), W, H) != RTOW_OK) return fail("write pfm");
+    if (exr && rtow_write_exr((out + ".exr").c_str(), rgb.data(), W, H) != RTOW_OK) return fail("write exr");
 
     double mean = 0;
     for (float v : rgb) mean += v;

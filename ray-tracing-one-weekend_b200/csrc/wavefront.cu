@@ -25,6 +25,7 @@
 namespace rtow {
 
 #define WF_FIXED_SCALE 4294967296.0   // 2^32: radiance sums in Q31.32
+#define WF_FIXED_SQ_SCALE 1048576.0   // 2^20: sums of squares in Q43.20
 
 // 256-bit global accesses (LDG.E.256 / STG.E.256); p must be 32-byte aligned
 __device__ __forceinline__ void ld256(const void *p, float4 &a, float4 &b) {
@@ -215,8 +216,11 @@ __device__ __forceinline__ void wf_add_pixel(const WavefrontLaunch &W, int pixel
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const float v = L[k];
-        if (v != 0.f && fabsf(v) <= 1e9f)      // NaN / inf / absurd radiance never reaches the sum (reference: undefined, main.cpp:963)
+        if (v != 0.f && fabsf(v) <= 1e9f) {    // NaN / inf / absurd radiance never reaches the sum (reference: undefined, main.cpp:963)
             atomicAdd(&W.fixed[(size_t)pixel * 3 + k], (unsigned long long)__double2ll_rn((double)v * WF_FIXED_SCALE));
+            if (W.fixed_sq && fabsf(v) <= 1e6f)
+                atomicAdd(&W.fixed_sq[(size_t)pixel * 3 + k], (unsigned long long)__double2ll_rn((double)v * (double)v * WF_FIXED_SQ_SCALE));
+        }
     }
 }
 
@@ -312,15 +316,15 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DScene S, WavefrontLaunch
     wf_refill(W, cam, ended, valid ? slot : 0, dead);
 }
 
-__global__ void wf_finalize_kernel(const unsigned long long *__restrict__ fixed, float *__restrict__ accum, size_t n) {
+__global__ void wf_finalize_kernel(const unsigned long long *__restrict__ fixed, float *__restrict__ accum, size_t n, double inv_scale) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const long long q = (long long)fixed[i];
-    accum[i] += (float)((double)q * (1.0 / WF_FIXED_SCALE));
+    accum[i] += (float)((double)q * inv_scale);
 }
 
 // ---- host driver ---------------------------------------------------------------------------------------------
-cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaunch &W, float *d_accum, unsigned long long *h_pinned,
+cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaunch &W, float *d_accum, float *d_accum_sq, unsigned long long *h_pinned,
                           cudaStream_t stream, uint32_t *launches_out, WavefrontProfile *prof) {
     // Lane refill pays when traversals are long (a million spheres: ~55 node visits per ray); on a scene of a few dozen
     // nodes a ray takes ~3 steps and the refill's load latency would dominate, so a warp then simply runs batches of 32
@@ -344,6 +348,7 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
     uint32_t launches = 0;
 
     cudaMemsetAsync(W.fixed, 0, n_acc * sizeof(unsigned long long), stream);
+    if (W.fixed_sq) cudaMemsetAsync(W.fixed_sq, 0, n_acc * sizeof(unsigned long long), stream);
     cudaMemsetAsync(W.control, 0, RTOW_WF_CONTROL_WORDS * sizeof(unsigned long long), stream);
     cudaMemsetAsync(W.counts, 0, 2 * RTOW_WF_MAX_CLASSES * sizeof(unsigned), stream);
     wf_generate_kernel<<<pool_blocks, 256, 0, stream>>>(W, cam);
@@ -376,10 +381,14 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
             if (*h_pinned >= (unsigned long long)W.pool) break;
         }
     }
-    wf_finalize_kernel<<<(unsigned)((n_acc + 255) / 256), 256, 0, stream>>>(W.fixed, d_accum, n_acc);
+    wf_finalize_kernel<<<(unsigned)((n_acc + 255) / 256), 256, 0, stream>>>(W.fixed, d_accum, n_acc, 1.0 / WF_FIXED_SCALE);
     launches++;
+    if (W.fixed_sq && d_accum_sq) {
+        wf_finalize_kernel<<<(unsigned)((n_acc + 255) / 256), 256, 0, stream>>>(W.fixed_sq, d_accum_sq, n_acc, 1.0 / WF_FIXED_SQ_SCALE);
+        launches++;
+    }
     if (launches_out) *launches_out = launches;
-    if (prof) { prof->iterations = (uint32_t)((launches - 2) / 2); prof->pool = (uint32_t)W.pool; for (auto &e : ev) cudaEventDestroy(e); }
+    if (prof) { prof->iterations = (uint32_t)((launches - 2 - (W.fixed_sq && d_accum_sq ? 1 : 0)) / 2); prof->pool = (uint32_t)W.pool; for (auto &e : ev) cudaEventDestroy(e); }
     return cudaGetLastError();
 }
 

@@ -60,6 +60,60 @@ def test_host_entry_points_work_without_a_device(pkg, abi, tmp_path):
     assert pfm.startswith(b"PF\n6 4\n-1.0\n") and np.array_equal(np.frombuffer(pfm[12:], dtype="<f4").reshape(4, 6, 3)[::-1], img)
 
 
+def _read_exr(path):
+    """Minimal reader for single-part, uncompressed, FLOAT scanline OpenEXR (the subset rtow_write_exr emits)."""
+    import struct
+    b = open(path, "rb").read()
+    assert struct.unpack_from("<ii", b, 0) == (20000630, 2)
+    pos, attrs = 8, {}
+    while b[pos] != 0:
+        e = b.index(b"\0", pos); name = b[pos:e].decode(); pos = e + 1
+        e = b.index(b"\0", pos); typ = b[pos:e].decode(); pos = e + 1
+        size, = struct.unpack_from("<i", b, pos); pos += 4
+        attrs[name] = (typ, b[pos:pos + size]); pos += size
+    pos += 1
+    chans, q, raw = [], 0, attrs["channels"][1]
+    while raw[q] != 0:
+        e = raw.index(b"\0", q); nm = raw[q:e].decode(); q = e + 1
+        ptype, plin, xs, ys = struct.unpack_from("<iiii", raw, q); q += 16
+        assert ptype == 2 and xs == ys == 1
+        chans.append(nm)
+    x0, y0, x1, y1 = struct.unpack("<iiii", attrs["dataWindow"][1])
+    W, H = x1 - x0 + 1, y1 - y0 + 1
+    assert attrs["compression"][1] == b"\0" and attrs["lineOrder"][1] == b"\0" and attrs["displayWindow"][1] == attrs["dataWindow"][1]
+    offs = struct.unpack_from("<%dQ" % H, b, pos)
+    img = np.zeros((H, W, 3), dtype=np.float32)
+    for row, off in enumerate(offs):
+        y, size = struct.unpack_from("<ii", b, off)
+        assert y == row and size == W * 4 * len(chans)
+        data = np.frombuffer(b, dtype="<f4", count=W * len(chans), offset=off + 8).reshape(len(chans), W)
+        for c, nm in enumerate(chans):
+            img[row, :, "RGB".index(nm)] = data[c]
+    assert offs[-1] + 8 + W * 4 * len(chans) == len(b)
+    return chans, img
+
+
+def test_exr_writer_and_oriented_camera(pkg, abi, tmp_path):
+    """hand-rolled OpenEXR output; per-frame camera update (camera.h:166-229) as a fresh POD."""
+    img = np.random.default_rng(3).uniform(0, 9, (5, 7, 3)).astype(np.float32)
+    pkg.write_exr(tmp_path / "a.exr", img)
+    chans, back = _read_exr(tmp_path / "a.exr")
+    assert chans == ["B", "G", "R"] and np.array_equal(back, img)
+    with pytest.raises(pkg.RtowError):
+        pkg.write_exr(tmp_path / "no_such_dir" / "a.exr", img)
+    # the constructor's hard-coded NED frame (camera.h:76-81) passed explicitly gives main()'s camera back, byte for byte
+    ned = np.array([[-1, 0, 0, 0], [0, 1, 0, 0], [0, 0, -1, 0], [0, 0, 0, 1]], dtype=np.float32)
+    assert bytes(pkg.oriented_camera((0, 0, 0), ned, 60.0, 16 / 9)) == bytes(pkg.main_camera(1920, 1080))
+    # a yaw of the frame and a moved eye change origin and screen vectors but not their lengths
+    c, s_ = np.cos(0.3), np.sin(0.3)
+    yaw = np.array([[-c, s_, 0, 0], [s_, c, 0, 0], [0, 0, -1, 0], [0, 0, 0, 1]], dtype=np.float32)
+    a, b = pkg.main_camera(1920, 1080), pkg.oriented_camera((5, -2, 1), yaw, 60.0, 16 / 9)
+    fa, fb = np.frombuffer(bytes(a), dtype=np.float32), np.frombuffer(bytes(b), dtype=np.float32)
+    assert not np.array_equal(fa, fb)
+    assert np.allclose(fb[0:3], (5, -2, 1))
+    assert np.isclose(np.linalg.norm(fa[6:9]), np.linalg.norm(fb[6:9]), rtol=1e-6) and np.isclose(np.linalg.norm(fa[9:12]), np.linalg.norm(fb[9:12]), rtol=1e-6)
+
+
 def test_compute_fails_loudly_without_a_device(pkg, abi):
     if pkg.lib().rtow_device_count() > 0:
         pytest.skip("a CUDA device is visible")

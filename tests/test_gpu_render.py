@@ -38,6 +38,27 @@ def test_render_matches_oracle(gpu, abi, port, name, kw, kernel):
     assert rmse <= 1e-3, f"{name}: RMSE {rmse}"
 
 
+def test_camera_moves_without_reuploading_the_scene(gpu, abi, port):
+    """the reference's fly-camera (main.cpp:485-642) only changes the camera; one DeviceScene, a fresh
+    rtow_camera per frame (Camera::setLookFromPoint + setOrientationMatrix), every frame equal to the oracle's."""
+    host = gpu.HostScene("cornell_ned", seed=12345)
+    dev = gpu.DeviceScene(host.desc)
+    W, H, spp = 80, 60, 4
+    params = abi.default_render_params(W, H, spp, seed=11)
+    frames = []
+    for k, (eye, ang) in enumerate([((0, 0, 0), 0.0), ((40, 30, -20), 0.25), ((120, -60, 10), -0.4)]):
+        c, s_ = np.cos(ang), np.sin(ang)
+        m = np.array([[-c, s_, 0, 0], [s_, c, 0, 0], [0, 0, -1, 0], [0, 0, 0, 1]], dtype=np.float32)
+        cam = gpu.oriented_camera(eye, m, 60.0, W / H)
+        img, st = dev.render(cam, params)
+        want = port.render(host.desc, cam, params)
+        assert st.rays == want["rays"], f"frame {k}"
+        ref = want["sum"] / np.float32(spp)
+        assert np.abs(img - ref).max() <= 2e-4 * max(1.0, float(ref.max())), f"frame {k}"
+        frames.append(img)
+    assert not np.array_equal(frames[0], frames[1]) and not np.array_equal(frames[1], frames[2])
+
+
 @pytest.mark.parametrize("kernel", [1, 2])
 def test_depth_limit_and_no_global_illum(gpu, abi, port, kernel):
     for depth, gi in ((0, 1), (1, 1), (3, 0)):
@@ -96,6 +117,39 @@ def test_render_is_deterministic_and_shard_invariant(gpu, abi):
     assert np.allclose(rgb.cpu().numpy(), a, rtol=1e-5, atol=1e-6)
 
 
+def test_progressive_moments_checkpoint_and_resume(gpu, abi, port, tmp_path):
+    """sums and sums of squares stay on the device across passes; two passes with a checkpoint in
+    between are the same sample set as one pass; the second moment equals the oracle's (same Philox streams)."""
+    import torch
+    host = gpu.HostScene("cornell_smoke_ned", seed=12345)
+    dev = gpu.DeviceScene(host.desc)
+    W, H = 64, 36
+    cam = gpu.main_camera(W, H)
+    pr = gpu.ProgressiveRender(dev, cam, W, H, seed=21)
+    st = pr.add(6)
+    assert st.paths == W * H * 6
+    pr.save(tmp_path / "ckpt.npz")
+    del pr
+    pr = gpu.ProgressiveRender.load(tmp_path / "ckpt.npz", dev, cam)
+    assert pr.n == 6
+    pr.add(10)
+    params = abi.default_render_params(W, H, 16, seed=21)
+    want = port.render(host.desc, cam, params, want_sumsq=True)
+    got_sum, got_sq = pr.sum.cpu().numpy(), pr.sumsq.cpu().numpy()
+    scale = max(1.0, float(want["sum"].max()))
+    assert np.abs(got_sum - want["sum"]).max() <= 2e-4 * scale
+    assert np.allclose(got_sq, want["sumsq"], rtol=2e-4, atol=1e-4 * max(1.0, float(want["sumsq"].max())))
+    var = pr.variance_of_mean()
+    assert var.shape == (H, W, 3) and np.all(var >= 0) and var.max() > 0
+    assert np.allclose(pr.mean(), want["sum"] / np.float32(16), atol=2e-4 * scale)
+    # the megakernel has no second-moment path: a loud error, not a silent zero image
+    acc = torch.zeros(H, W, 3, dtype=torch.float32, device="cuda:0")
+    with pytest.raises(gpu.RtowError) as e:
+        dev.accumulate_moments_device(cam, abi.default_render_params(W, H, 4, seed=1, kernel=abi.KERNEL_MEGA), acc.data_ptr(), acc.data_ptr(),
+                                      torch.cuda.current_stream().cuda_stream)
+    assert e.value.code == abi.ERR_UNSUPPORTED
+
+
 def test_bgra8_matches_reference_tone_curve(gpu, abi, ob):
     host = gpu.HostScene("cornell_ned", seed=3)
     dev = gpu.DeviceScene(host.desc)
@@ -134,8 +188,8 @@ def test_headless_cli_writes_ppm_pfm_and_stats(gpu, abi, tmp_path):
     import subprocess
     cli = os.path.join(os.path.dirname(gpu.lib_path()), "rtow_cli")
     prefix = str(tmp_path / "f")
-    out = subprocess.run([cli, "--scene", "cornell_smoke_ned", "--width", "64", "--height", "36", "--spp", "8", "--seed", "5", "--out", prefix],
-                         capture_output=True, text=True)
+    out = subprocess.run([cli, "--scene", "cornell_smoke_ned", "--width", "64", "--height", "36", "--spp", "8", "--seed", "5", "--out", prefix,
+                          "--exr"], capture_output=True, text=True)
     assert out.returncode == 0, out.stderr
     st = json.loads(out.stdout.strip().splitlines()[-1])
     assert st["paths"] == 64 * 36 * 8 and st["rays"] > st["paths"] and st["mean_radiance"] > 0
@@ -145,6 +199,9 @@ def test_headless_cli_writes_ppm_pfm_and_stats(gpu, abi, tmp_path):
     ppm = open(prefix + ".ppm", "rb").read()
     want = np.minimum((255.99 * np.sqrt(rgb).astype(np.float64)).astype(np.int64), 255).astype(np.uint8)
     assert ppm[len(b"P6\n64 36\n255\n"):] == want.tobytes()
+    from test_abi_surface import _read_exr
+    chans, exr = _read_exr(prefix + ".exr")
+    assert chans == ["B", "G", "R"] and np.array_equal(exr, rgb)
     # the same frame through the Python binding
     host = gpu.HostScene("cornell_smoke_ned", seed=12345)
     img, _ = gpu.DeviceScene(host.desc).render(gpu.main_camera(64, 36), abi.default_render_params(64, 36, 8, seed=5))
