@@ -114,6 +114,52 @@ def test_exr_writer_and_oriented_camera(pkg, abi, tmp_path):
     assert np.isclose(np.linalg.norm(fa[6:9]), np.linalg.norm(fb[6:9]), rtol=1e-6) and np.isclose(np.linalg.norm(fa[9:12]), np.linalg.norm(fb[9:12]), rtol=1e-6)
 
 
+def test_cpp_convenience_layer_compiles(pkg, tmp_path):
+    """include/rtow/render.h (the C++ convenience over the C ABI): the example builds and links against the
+    library, and -- where the reference sources exist -- the same header instantiates on the reference's OWN classes, which
+    is the binding INTEGRATION.md tells a maintainer to add."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    libdir = os.path.dirname(pkg.lib_path())
+    exe = str(tmp_path / "render_api")
+    r = subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", os.path.join(root, "examples", "render_api.cpp"), "-I" + os.path.join(root, "include"),
+                        "-L" + libdir, "-lrtow_b200", "-Wl,-rpath," + libdir, "-Wl,-rpath-link,/usr/local/cuda/lib64", "-o", exe],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    if pkg.lib().rtow_device_count() == 0:
+        run = subprocess.run([exe, "32", "18", "2"], capture_output=True, text=True)
+        assert run.returncode == 1 and "no CPU path" in run.stderr
+    ref = "/root/reference/rayTracingOneWeekend"
+    if not os.path.isdir(ref):
+        return
+    tu = tmp_path / "ref_binding.cpp"
+    tu.write_text("""
+#include <cfloat>
+#include "scenes.h"
+#include "rtow/render.h"
+struct RefTraits {
+    using vec3 = ::vec3; using Hitable = ::Hitable; using Material = ::Material; using Texture = ::Texture;
+    using FlipNormals = ::FlipNormals; using Translate = ::Translate; using RotateY = ::RotateY;
+    using Sphere = ::Sphere; using MovingSphere = ::MovingSphere;
+    using XYRectangle = ::XYRectangle; using XZRectangle = ::XZRectangle; using YZRectangle = ::YZRectangle;
+    using Box = ::Box; using ConstantMedium = ::ConstantMedium; using HitableList = ::HitableList; using BvhNode = ::BvhNode;
+    using Lambertian = ::Lambertian; using Metal = ::Metal; using Dielectric = ::Dielectric;
+    using DiffuseLight = ::DiffuseLight; using Isotropic = ::Isotropic;
+    using ConstantTexture = ::ConstantTexture; using CheckerTexture = ::CheckerTexture;
+    using NoiseTexture = ::NoiseTexture; using ImageTexture = ::ImageTexture;
+    using Perlin = ::Perlin; using Camera = ::Camera;
+    static double unif01() { return unifRand(randomNumberGenerator); }
+};
+rtow_stats frame(Hitable *world, Camera *cam, rtow::Image &out) {
+    rtow::DeviceWorld<RefTraits> gpu(world);
+    return gpu.render(*cam, rtow::default_params(800, 800, 64), out);
+}
+""")
+    r = subprocess.run(["g++", "-std=c++17", "-w", "-fsyntax-only", str(tu), "-I" + ref, "-I" + os.path.join(root, "include")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+
+
 def test_compute_fails_loudly_without_a_device(pkg, abi):
     if pkg.lib().rtow_device_count() > 0:
         pytest.skip("a CUDA device is visible")

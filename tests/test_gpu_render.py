@@ -117,6 +117,28 @@ def test_render_is_deterministic_and_shard_invariant(gpu, abi):
     assert np.allclose(rgb.cpu().numpy(), a, rtol=1e-5, atol=1e-6)
 
 
+def test_cpp_convenience_layer_renders(gpu, abi, tmp_path):
+    """examples/render_api.cpp: scene built with the mirror scene API, flattened, uploaded once, two frames with a camera
+    move in between, all through include/rtow/render.h.  The first frame equals the same render through ctypes."""
+    import json
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    libdir = os.path.dirname(gpu.lib_path())
+    exe = str(tmp_path / "render_api")
+    r = subprocess.run(["g++", "-std=c++17", "-O1", os.path.join(root, "examples", "render_api.cpp"), "-I" + os.path.join(root, "include"),
+                        "-L" + libdir, "-lrtow_b200", "-Wl,-rpath," + libdir, "-Wl,-rpath-link,/usr/local/cuda/lib64", "-o", exe],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    run = subprocess.run([exe, "64", "36", "4"], capture_output=True, text=True)
+    assert run.returncode == 0, run.stderr
+    st = json.loads(run.stdout.strip().splitlines()[-1])
+    assert st["paths"] == [64 * 36 * 4] * 2 and min(st["rays"]) > 64 * 36 * 4 and st["mean"][0] != st["mean"][1]
+    host = gpu.HostScene("cornell_ned", seed=12345)
+    img, s0 = gpu.DeviceScene(host.desc).render(gpu.main_camera(64, 36), abi.default_render_params(64, 36, 4, seed=5))
+    assert s0.rays == st["rays"][0] and abs(float(img.mean()) - st["mean"][0]) < 1e-5
+
+
 def test_progressive_moments_checkpoint_and_resume(gpu, abi, port, tmp_path):
     """sums and sums of squares stay on the device across passes; two passes with a checkpoint in
     between are the same sample set as one pass; the second moment equals the oracle's (same Philox streams)."""
