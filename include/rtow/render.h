@@ -59,9 +59,10 @@ public:
     // its 28-float POD is rebuilt, the scene stays on the device.
     rtow_stats render(typename Traits::Camera &cam, const rtow_render_params &params, Image &out, bool dof_enabled = false) {
         const rtow_camera pod = camera_pod<Traits>(cam, dof_enabled);
-        out.width = params.width; out.height = params.height;
-        out.rgb.resize((size_t)params.width * params.height * 3);
-        out.bgra.resize((size_t)params.width * params.height * 4);
+        out.width = params.width;
+        out.height = params.row_count > 0 ? params.row_count : params.height;     // a band of rows gives a band-sized image
+        out.rgb.resize((size_t)out.width * out.height * 3);
+        out.bgra.resize((size_t)out.width * out.height * 4);
         rtow_stats st = {};
         check(rtow_render(scene_, &pod, &params, out.rgb.data(), out.bgra.data(), &st));
         return st;

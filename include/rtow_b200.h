@@ -214,7 +214,11 @@ typedef struct rtow_render_params {
     float ambient_gain;         /* GLOBAL_ILLUM_GAIN defines.h:25 */
     int32_t kernel;             /* RTOW_KERNEL_* */
     int32_t traverse;           /* RTOW_TRAVERSE_* */
-    int32_t reserved[4];
+    int32_t row_begin;          /* image-tile partitioning (SURVEY 8(e) "partitioning 2"): render only image rows */
+    int32_t row_count;          /* [row_begin, row_begin+row_count), row 0 = top; 0 = the whole frame.  With a band the
+                                 * accumulators passed to rtow_render_accumulate*_device are BAND-sized (row_count*W*3 floats,
+                                 * band-local indexing); pixels keep their full-frame Philox keys, so bands tile the same image */
+    int32_t reserved[2];
 } rtow_render_params;
 
 typedef struct rtow_stats {
@@ -245,7 +249,8 @@ int rtow_trace_rays(rtow_scene *scene, const rtow_ray *rays, uint64_t n, rtow_hi
 int rtow_trace_rays_device(rtow_scene *scene, const rtow_ray *d_rays, uint64_t n, rtow_hit *d_hits,
                            int traverse, uint64_t seed, void *stream);
 
-/* Full image: rgb_linear_out = W*H*3 floats, mean linear radiance, row 0 = top of image
+/* Full image (or the band of rows params->row_begin/row_count, outputs then band-sized):
+ * rgb_linear_out = W*H*3 floats, mean linear radiance, row 0 = top of image
  * (main.cpp:982-984 writes row H-1 first); bgra8_out (nullable) = W*H*4 bytes B,G,R,0 after
  * the sqrt tone curve (main.cpp:955-989). */
 int rtow_render(rtow_scene *scene, const rtow_camera *cam, const rtow_render_params *params,

@@ -110,7 +110,9 @@ class RenderParams(C.Structure):
         ("ambient_gain", C.c_float),
         ("kernel", C.c_int32),
         ("traverse", C.c_int32),
-        ("reserved", C.c_int32 * 4),
+        ("row_begin", C.c_int32),
+        ("row_count", C.c_int32),
+        ("reserved", C.c_int32 * 2),
     ]
 
 
@@ -152,7 +154,7 @@ class WorkCounters(C.Structure):
 
 
 def default_render_params(width, height, spp, seed=1, max_depth=50, kernel=KERNEL_AUTO, traverse=TRAVERSE_AUTO,
-                          sample_begin=0, sample_count=0):
+                          sample_begin=0, sample_count=0, row_begin=0, row_count=0):
     """defines.h defaults: GLOBAL_ILLUM_EN 1, SKY_ILLUM_GAIN 1.0, GLOBAL_ILLUM_GAIN 0.3, DEPTH_RECURSION 50."""
     p = RenderParams()
     p.width, p.height, p.spp = width, height, spp
@@ -164,6 +166,7 @@ def default_render_params(width, height, spp, seed=1, max_depth=50, kernel=KERNE
     p.ambient_gain = 0.3
     p.kernel = kernel
     p.traverse = traverse
+    p.row_begin, p.row_count = row_begin, row_count
     return p
 
 

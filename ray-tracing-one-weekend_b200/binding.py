@@ -189,7 +189,7 @@ class DeviceScene:
 
     # -- the pixel loop -------------------------------------------------------------------
     def render(self, cam, params, want_bgra=False):
-        W, H = params.width, params.height
+        W, H = params.width, (params.row_count if params.row_count > 0 else params.height)    # a band of rows gives band-sized outputs
         rgb = np.zeros((H, W, 3), dtype=np.float32)
         bgra = np.zeros((H, W, 4), dtype=np.uint8) if want_bgra else None
         st = abi.Stats()

@@ -248,6 +248,11 @@ int check_render_args(const rtow_scene *s, const rtow_camera *cam, const rtow_re
     while (S > count) S >>= 1;
     L->lanes_per_pixel = S;
     L->traverse = trav;
+    if (p->row_begin < 0 || p->row_count < 0 || (long long)p->row_begin + p->row_count > p->height || (p->row_count == 0 && p->row_begin != 0))
+        return set_error(RTOW_ERR_INVALID_ARG, "render: row band outside the frame");
+    const int rows = p->row_count > 0 ? p->row_count : p->height;
+    L->pixel_begin = p->row_begin * p->width;
+    L->pixel_count = rows * p->width;
     L->sky_gain = p->sky_gain; L->ambient_gain = p->ambient_gain;
     L->seed = p->seed;
     return RTOW_OK;
@@ -517,7 +522,7 @@ int rtow_render_accumulate_moments_device(rtow_scene *s, const rtow_camera *cam,
     if (kernel == RTOW_KERNEL_WAVEFRONT) {
         // Synchronises `stream` internally (the host loop polls the pool for completion).
         static const long long pool_cap = [] { const char *e = getenv("RTOW_WF_POOL"); return e ? atoll(e) : (1ll << 20); }();
-        const long long n_pixels = (long long)L.width * L.height;
+        const long long n_pixels = (long long)L.pixel_count;
         const unsigned long long items = (unsigned long long)((n_pixels + 31) / 32) * 32ull * (unsigned)L.sample_count;
         long long pool = (long long)std::min<unsigned long long>(items, (unsigned long long)pool_cap);
         pool = (pool + 255) / 256 * 256;
@@ -612,7 +617,7 @@ int rtow_render(rtow_scene *s, const rtow_camera *cam, const rtow_render_params 
     if (int rc = check_render_args(s, cam, params, &L)) return rc;
     if (stats) std::memset(stats, 0, sizeof *stats);
     CUDA_TRY(cudaSetDevice(s->device));
-    size_t pixels = (size_t)params->width * params->height;
+    const size_t pixels = (size_t)L.pixel_count;        // the whole frame, or the requested band of rows (outputs are band-sized)
     if (int rc = ensure_image_buffers(s, pixels)) return rc;
     cudaStream_t st = s->stream;
     cudaEvent_t t0, t1;
@@ -621,7 +626,7 @@ int rtow_render(rtow_scene *s, const rtow_camera *cam, const rtow_render_params 
     CUDA_TRY(cudaMemsetAsync(s->d_accum, 0, pixels * 3 * sizeof(float), st));
     if (int rc = rtow_render_accumulate_device(s, cam, params, s->d_accum, st)) return rc;
     // the mean is over the samples this call rendered
-    launch_resolve(s->d_accum, params->width, params->height, L.sample_count, rgb_linear_out ? s->d_rgb : nullptr, bgra8_out ? s->d_bgra : nullptr, st);
+    launch_resolve(s->d_accum, params->width, L.pixel_count / params->width, L.sample_count, rgb_linear_out ? s->d_rgb : nullptr, bgra8_out ? s->d_bgra : nullptr, st);
     CUDA_TRY(cudaGetLastError());
     if (rgb_linear_out) CUDA_TRY(cudaMemcpyAsync(rgb_linear_out, s->d_rgb, pixels * 3 * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (bgra8_out) CUDA_TRY(cudaMemcpyAsync(bgra8_out, s->d_bgra, pixels * 4, cudaMemcpyDeviceToHost, st));

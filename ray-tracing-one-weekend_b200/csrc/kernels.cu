@@ -266,10 +266,11 @@ __global__ void __launch_bounds__(256) render_mega_kernel(DScene S, rtow_camera 
     const int ppw = 32 / Sl;                                  // pixels per warp
     const int lane = threadIdx.x & 31;
     const unsigned warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int n_pixels = L.width * L.height;
+    const int n_pixels = L.pixel_count;                       // this launch's band of rows
     const long long pixel_ll = (long long)warp_global * ppw + lane / Sl;
     const bool pixel_ok = pixel_ll < n_pixels;
-    const int pixel = pixel_ok ? (int)pixel_ll : 0;
+    const int pixel_local = pixel_ok ? (int)pixel_ll : 0;     // accumulator index
+    const int pixel = pixel_local + L.pixel_begin;            // full-frame index: camera sample position and Philox key
     const int lane_s = lane % Sl;
     const int x = pixel % L.width, y = pixel / L.width;
     const int row = L.height - 1 - y;                         // the reference counts rows from the bottom (main.cpp:932)
@@ -365,7 +366,7 @@ __global__ void __launch_bounds__(256) render_mega_kernel(DScene S, rtow_camera 
         acc[2] += __shfl_down_sync(0xffffffffu, acc[2], off);
     }
     if (pixel_ok && lane_s == 0) {
-        float *px = accum + (size_t)pixel * 3;
+        float *px = accum + (size_t)pixel_local * 3;
         px[0] += acc[0]; px[1] += acc[1]; px[2] += acc[2];
     }
     for (int off = 16; off; off >>= 1) {
@@ -389,7 +390,7 @@ __global__ void __launch_bounds__(256) render_mega_kernel(DScene S, rtow_camera 
 
 void launch_render_mega(const DScene &S, const rtow_camera &cam, const RenderLaunch &L, float *d_accum,
                         unsigned long long *d_counters, bool count, cudaStream_t stream) {
-    long long n_pixels = (long long)L.width * L.height;
+    long long n_pixels = (long long)L.pixel_count;
     int ppw = 32 / L.lanes_per_pixel;
     long long warps = (n_pixels + ppw - 1) / ppw;
     long long blocks = (warps + 7) / 8;

@@ -13,6 +13,8 @@ struct RenderLaunch {
     int32_t lanes_per_pixel;              // S: power of two <= 32; a warp owns 32/S pixels
     int32_t traverse;                     // RTOW_TRAVERSE_EXACT / _FAST
     float sky_gain, ambient_gain;
+    int32_t pixel_begin, pixel_count;     // this launch renders full-frame pixels [pixel_begin, +pixel_count) = a band of rows;
+                                          // accumulators are indexed by pixel - pixel_begin
     uint64_t seed;
 };
 

@@ -46,7 +46,7 @@ __device__ __forceinline__ void wf_item_to_pixel(const WavefrontLaunch &W, unsig
     // samples each.  Measured (B200, shade kernel per 2^20 slots): 0.085 ms this way; 0.125 ms with all pixels of one
     // sample in flight (the 64-bit pixel atomics then sweep 25 MB of accumulators); 0.135 ms with 1024 samples of only
     // 1024 pixels in flight (the atomics collide).
-    const unsigned long long padded = ((unsigned long long)W.L.width * (unsigned long long)W.L.height + 31ull) & ~31ull;
+    const unsigned long long padded = ((unsigned long long)W.L.pixel_count + 31ull) & ~31ull;      // pixels of this launch's band
     const unsigned long long full_blocks = (unsigned)W.L.sample_count / WF_SAMPLE_BLOCK;
     const unsigned long long full_items = full_blocks * padded * WF_SAMPLE_BLOCK;
     unsigned long long j = item, first = 0, bsz = WF_SAMPLE_BLOCK;
@@ -68,7 +68,8 @@ __device__ __forceinline__ void wf_item_to_pixel(const WavefrontLaunch &W, unsig
 __device__ __forceinline__ bool wf_start_path(const WavefrontLaunch &W, const rtow_camera &cam, unsigned long long item, int slot) {
     int pixel, s;
     wf_item_to_pixel(W, item, pixel, s);
-    if (pixel >= W.L.width * W.L.height) return false;
+    if (pixel >= W.L.pixel_count) return false;
+    pixel += W.L.pixel_begin;             // full-frame pixel index: camera sample position and Philox key
     const int x = pixel % W.L.width, y = pixel / W.L.width;
     const int row = W.L.height - 1 - y;
     Rng g;
@@ -217,9 +218,9 @@ __device__ __forceinline__ void wf_add_pixel(const WavefrontLaunch &W, int pixel
     for (int k = 0; k < 3; ++k) {
         const float v = L[k];
         if (v != 0.f && fabsf(v) <= 1e9f) {    // NaN / inf / absurd radiance never reaches the sum (reference: undefined, main.cpp:963)
-            atomicAdd(&W.fixed[(size_t)pixel * 3 + k], (unsigned long long)__double2ll_rn((double)v * WF_FIXED_SCALE));
+            atomicAdd(&W.fixed[(size_t)(pixel - W.L.pixel_begin) * 3 + k], (unsigned long long)__double2ll_rn((double)v * WF_FIXED_SCALE));
             if (W.fixed_sq && fabsf(v) <= 1e6f)
-                atomicAdd(&W.fixed_sq[(size_t)pixel * 3 + k], (unsigned long long)__double2ll_rn((double)v * (double)v * WF_FIXED_SQ_SCALE));
+                atomicAdd(&W.fixed_sq[(size_t)(pixel - W.L.pixel_begin) * 3 + k], (unsigned long long)__double2ll_rn((double)v * (double)v * WF_FIXED_SQ_SCALE));
         }
     }
 }
@@ -344,7 +345,7 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
     else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_extend_kernel<5>, 128, 0);
     const unsigned ext_blocks = (unsigned)std::min<long long>((W.pool + 127) / 128, (long long)sms * std::max(per_sm, 1));
     const unsigned pool_blocks = (unsigned)(W.pool / 256);
-    const size_t n_acc = (size_t)W.L.width * W.L.height * 3;
+    const size_t n_acc = (size_t)W.L.pixel_count * 3;
     uint32_t launches = 0;
 
     cudaMemsetAsync(W.fixed, 0, n_acc * sizeof(unsigned long long), stream);

@@ -172,6 +172,37 @@ def test_progressive_moments_checkpoint_and_resume(gpu, abi, port, tmp_path):
     assert e.value.code == abi.ERR_UNSUPPORTED
 
 
+@pytest.mark.parametrize("kernel", [1, 2], ids=["mega", "wavefront"])
+def test_row_bands_tile_the_full_frame(gpu, abi, kernel):
+    """SURVEY 8(e) partitioning 2: a band of rows rendered into a band-sized buffer holds exactly the rows of the full
+    frame (pixels keep their full-frame Philox keys and camera positions); interleaved bands from sharding.band_ranges."""
+    import torch
+    host = gpu.HostScene("random_ned", seed=12345, image=earth_image())
+    dev = gpu.DeviceScene(host.desc)
+    W, H, spp = 72, 41, 6
+    cam = gpu.main_camera(W, H)
+    stream = torch.cuda.current_stream().cuda_stream
+    full = torch.zeros(H, W, 3, dtype=torch.float32, device="cuda:0")
+    dev.accumulate_device(cam, abi.default_render_params(W, H, spp, seed=3, kernel=kernel), full.data_ptr(), stream)
+    torch.cuda.synchronize()
+    tiled = torch.zeros_like(full)
+    paths = 0
+    for rank in range(3):
+        for y, n in gpu.sharding.band_ranges(H, rank, 3, band_rows=8):
+            band = torch.zeros(n, W, 3, dtype=torch.float32, device="cuda:0")
+            dev.accumulate_device(cam, abi.default_render_params(W, H, spp, seed=3, kernel=kernel, row_begin=y, row_count=n), band.data_ptr(), stream)
+            paths += dev.stream_stats(stream).paths
+            tiled[y:y + n] = band
+    assert paths == W * H * spp
+    assert torch.equal(tiled, full)
+    # host-buffer entry point with a band: band-sized outputs
+    img, st = dev.render(cam, abi.default_render_params(W, H, spp, seed=3, kernel=kernel, row_begin=16, row_count=9))
+    assert img.shape == (9, W, 3) and st.paths == 9 * W * spp
+    assert np.array_equal(img, (full[16:25] * np.float32(1.0 / spp)).cpu().numpy())
+    with pytest.raises(gpu.RtowError):
+        dev.render(cam, abi.default_render_params(W, H, spp, row_begin=40, row_count=5))
+
+
 def test_bgra8_matches_reference_tone_curve(gpu, abi, ob):
     host = gpu.HostScene("cornell_ned", seed=3)
     dev = gpu.DeviceScene(host.desc)
