@@ -339,7 +339,7 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
         float4 *nd = &out.nodes[id * FAST_NODE_F4];
         nd[0] = make_float4(p[0], p[1], p[2], i2f((int32_t)(ebyte[0] | ebyte[1] << 8 | ebyte[2] << 16)));
         nd[1] = make_float4(i2f((int32_t)qlo[0]), i2f((int32_t)qlo[1]), i2f((int32_t)qlo[2]), i2f((int32_t)qhi[0]));
-        nd[2] = make_float4(i2f((int32_t)qhi[1]), i2f((int32_t)qhi[2]), 0.f, 0.f);
+        nd[2] = make_float4(i2f((int32_t)qhi[1]), i2f((int32_t)qhi[2]), i2f((int32_t)FAST_NODE_BIAS_WORD), 0.f);
         nd[3] = make_float4(i2f(w.ref[0]), i2f(w.ref[1]), i2f(w.ref[2]), i2f(w.ref[3]));
     }
     return true;

@@ -26,13 +26,14 @@ namespace rtow {
 // closest-hit kernel is bound by.  Decoded boxes contain the float boxes (lo rounded down, hi up): culling only.
 //   [0] origin p.xyz (float), exponent bytes ex | ey << 8 | ez << 16 (biased: cell size = 2^(e-127))
 //   [1] lo.x, lo.y, lo.z, hi.x   each word = the 4 children's bytes (child k in bits 8k..8k+7)
-//   [2] hi.y, hi.z, -, -
+//   [2] hi.y, hi.z, FAST_NODE_BIAS_WORD (the byte decoder's 2^15 float pattern, see rt_fast.cuh byte_f), -
 //   [3] child refs as int bits: >= 0 node index; < 0 leaf, ~ref = object id | FAST_LEAF_* flags; FAST_EMPTY = no child
 // Per object (leaf), indexed by object id:
 //   spheres[obj]        {cx,cy,cz,r} of a bare Sphere leaf (FAST_LEAF_SPHERE), else zeros
 //   guards[2*obj..+1]   {bmin.xyz, -} {bmax.xyz, -}: box of the reference BvhNode that owns the leaf
 enum { FAST_NODE_F4 = 4 };
 static const int32_t FAST_EMPTY = 0x7fffffff;
+static const uint32_t FAST_NODE_BIAS_WORD = 0x47000000u;
 enum {
     FAST_LEAF_SPHERE = 1 << 30,   // the object is one untransformed Sphere: test spheres[obj] directly
     FAST_LEAF_TWICE = 1 << 29,    // n==1 node holding a medium: the reference evaluates it twice (bvhNode.h:38-40,70-71)

@@ -86,14 +86,12 @@ __global__ void __launch_bounds__(256) trace_kernel(DScene S, const rtow_ray *__
 template <bool COUNT, int MINB>
 __global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, const rtow_ray *__restrict__ rays, uint64_t n, rtow_hit *__restrict__ hits,
                                                                uint64_t seed, unsigned long long *__restrict__ counters,
-                                                               unsigned long long *__restrict__ queue_head, int refill_below, int leaf_min, int pop_tries) {
+                                                               unsigned long long *__restrict__ queue_head, int refill_below, int leaf_min) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    __shared__ int s_ref[RTOW_TRACE_STACK_SMEM * 128];
-    __shared__ float s_d[RTOW_TRACE_STACK_SMEM * 128];
+    __shared__ uint2 s_stack[RTOW_TRACE_STACK_SMEM * 128];
     SmemStack<RTOW_TRACE_STACK_SMEM> st;
-    st.sref = s_ref + (threadIdx.x >> 5) * (RTOW_TRACE_STACK_SMEM * 32) + lane;
-    st.sd = s_d + (threadIdx.x >> 5) * (RTOW_TRACE_STACK_SMEM * 32) + lane;
+    st.col = s_stack + (threadIdx.x >> 5) * (RTOW_TRACE_STACK_SMEM * 32) + lane;
     FastTrav T;
     T.cur = RTOW_TRAV_DONE; T.sp = 0;
     uint64_t idx = 0;
@@ -144,7 +142,7 @@ __global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, c
         // a 4-wide node step or a leaf test -- for the lanes that are at that kind; the others wait a round.
         // Leaves are taken once `leaf_min` lanes wait at one (or nobody is at a node).
         for (;;) {
-            for (int a = 0; a < pop_tries; ++a) fast_pop_one(T, st);     // a stale entry costs a pop, not a round
+            fast_pop(T, st);
             const bool at_node = fast_at_node(T), at_leaf = fast_at_leaf(T);
             const unsigned mn = __ballot_sync(full, at_node), ml = __ballot_sync(full, at_leaf);
             const unsigned alive = __ballot_sync(full, T.cur != RTOW_TRAV_DONE);
@@ -228,12 +226,11 @@ void launch_trace(const DScene &S, const rtow_ray *d_rays, uint64_t n, rtow_hit 
         static const int refill_env = [] { const char *e = getenv("RTOW_TRACE_REFILL"); return e ? atoi(e) : -1; }();
         const int refill = refill_env >= 0 ? refill_env : (S.fast_n_nodes >= 4096 ? RTOW_REFILL_BELOW : 1);   // see run_wavefront
         static const int leaf_min = [] { const char *e = getenv("RTOW_TRACE_LEAFMIN"); return e ? atoi(e) : 8; }();
-        static const int pops = [] { const char *e = getenv("RTOW_TRACE_POPS"); return e ? atoi(e) : 1; }();
         auto go = [&](auto kern) {
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, 0);
             unsigned long long want = (n + 127) / 128;
             unsigned blocks = (unsigned)std::min<unsigned long long>(want, (unsigned long long)sms * (unsigned)std::max(per_sm, 1));
-            kern<<<blocks, 128, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters, head, refill, leaf_min, pops);
+            kern<<<blocks, 128, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters, head, refill, leaf_min);
             unsigned fb = (unsigned)((n + 255) / 256);
             if (count) trace_finish_kernel<true><<<fb, 256, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters);
             else trace_finish_kernel<false><<<fb, 256, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters);

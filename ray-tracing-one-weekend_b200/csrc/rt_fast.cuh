@@ -54,8 +54,11 @@ __device__ __forceinline__ float4 sel4(bool c, const float4 &a, const float4 &b)
 // byte k of w as the float 32768 + q, with one PRMT (no I2F, no subtraction): 0x4700qq00 is 2^15 + q exactly.  The
 // builder folds the -32768 cells into the stored node origin (fast_bvh.cpp) and widens every plane by cell/64, which
 // covers the cell/512-sized roundings this leaves in the plane distances.
-__device__ __forceinline__ float byte_f(unsigned w, int k) {
-    return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7404 + (k << 4)));
+// `hi` is the word 0x47000000, which every node carries in a spare slot: taken from the register the node load just
+// filled, it leaves the selector as the instruction's immediate (given the literal, ptxas keeps the four selectors in
+// registers instead and re-materialises them with ~26 moves per node).
+__device__ __forceinline__ float byte_f(unsigned w, unsigned hi, int k) {
+    return __uint_as_float(__byte_perm(w, hi, 0x7404 + (k << 4)));
 }
 
 __device__ __forceinline__ float lane4(const float4 &v, int k) { return k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w; }
@@ -98,15 +101,15 @@ __device__ __forceinline__ void fast_begin(const DScene &S, const Ray &r, float 
     T.cur = S.fast_root; T.sp = 0;
 }
 
-// Traversal stacks.  LocalStack lives in thread-local memory (an access with lanes at different depths costs one L1
-// wavefront per distinct depth).  SmemStack keeps the top CAP entries in shared memory, one 4-byte column per lane
-// (bank = lane: any mix of depths is one conflict-free wavefront), and only deeper entries in local memory.
+// Traversal stacks.  An entry is {child ref, entry distance} in one 8-byte word pair, moved with one 64-bit access.
+// LocalStack lives in thread-local memory (an access with lanes at different depths costs one L1 wavefront per
+// distinct depth).  SmemStack keeps the top CAP entries in shared memory, one 8-byte column per lane (entry i of lane
+// l at word pair i*32 + l: whatever the mix of depths, a warp's access is the two wavefronts 256 bytes need anyway),
+// and only deeper entries in local memory.
 struct LocalStack {
-    int ref[RTOW_FAST_STACK];
-    float d[RTOW_FAST_STACK];
-    __device__ __forceinline__ void put(int i, int r, float dist) { ref[i] = r; d[i] = dist; }
-    __device__ __forceinline__ float dist(int i) const { return d[i]; }
-    __device__ __forceinline__ int node(int i) const { return ref[i]; }
+    uint2 e[RTOW_FAST_STACK];
+    __device__ __forceinline__ void put(int i, int r, float dist) { e[i] = make_uint2((unsigned)r, __float_as_uint(dist)); }
+    __device__ __forceinline__ uint2 get(int i) const { return e[i]; }
     // entries 1..3 of a sorted child list (d1 <= d2 <= d3, culled ones = +inf), pushed far-to-near
     __device__ __forceinline__ int push3(int sp, const int *r, const float *dd) {
         const float inf = __int_as_float(0x7f800000);
@@ -118,26 +121,24 @@ struct LocalStack {
 };
 template <int CAP>
 struct SmemStack {
-    int *sref;      // this lane's column: entry i at sref[i * 32]
-    float *sd;
-    int lref[RTOW_FAST_STACK - CAP];
-    float ld[RTOW_FAST_STACK - CAP];
+    uint2 *col;     // this lane's column: entry i at col[i * 32]
+    uint2 loc[RTOW_FAST_STACK - CAP];
     __device__ __forceinline__ void put(int i, int r, float dist) {
-        if (i < CAP) { sref[i * 32] = r; sd[i * 32] = dist; } else { lref[i - CAP] = r; ld[i - CAP] = dist; }
+        const uint2 v = make_uint2((unsigned)r, __float_as_uint(dist));
+        if (i < CAP) col[i * 32] = v; else loc[i - CAP] = v;
     }
-    __device__ __forceinline__ float dist(int i) const { return i < CAP ? sd[i * 32] : ld[i - CAP]; }
-    __device__ __forceinline__ int node(int i) const { return i < CAP ? sref[i * 32] : lref[i - CAP]; }
+    __device__ __forceinline__ uint2 get(int i) const { return i < CAP ? col[i * 32] : loc[i - CAP]; }
     // Branch-free in the common case (all three slots in shared memory): every candidate is stored, and the slot index
     // only advances past the live ones -- a culled entry (they sort last) is overwritten by the next store.
     __device__ __forceinline__ int push3(int sp, const int *r, const float *dd) {
         const float inf = __int_as_float(0x7f800000);
         if (sp + 3 <= CAP) {
-            int *pr = sref + sp * 32; float *pd = sd + sp * 32;
-            pr[0] = r[3]; pd[0] = dd[3];
+            uint2 *p = col + sp * 32;
+            p[0] = make_uint2((unsigned)r[3], __float_as_uint(dd[3]));
             int k = dd[3] < inf ? 32 : 0;
-            pr[k] = r[2]; pd[k] = dd[2];
+            p[k] = make_uint2((unsigned)r[2], __float_as_uint(dd[2]));
             k += dd[2] < inf ? 32 : 0;
-            pr[k] = r[1]; pd[k] = dd[1];
+            p[k] = make_uint2((unsigned)r[1], __float_as_uint(dd[1]));
             return sp + (k >> 5) + (dd[1] < inf ? 1 : 0);
         }
         if (dd[3] < inf) put(sp++, r[3], dd[3]);
@@ -147,14 +148,19 @@ struct SmemStack {
     }
 };
 
-// One pop attempt: the next stacked subtree if it can still hold a hit with t <= best, else stay in POP state.
-// (One entry per call, so that a warp's lanes pop in lock-step instead of looping individually over stale entries.)
+// Pop: the nearest stacked subtree that can still hold a hit with t <= best; stale entries (pushed before the ray
+// found its current best) are skipped in a tight loop -- a handful of instructions each, where a voting round of the
+// persistent kernels costs ~50 -- and a lane whose stack runs out is done.
 template <class STACK>
-__device__ __forceinline__ void fast_pop_one(FastTrav &T, const STACK &st) {
+__device__ __forceinline__ void fast_pop(FastTrav &T, const STACK &st) {
     if (T.cur != RTOW_TRAV_POP) return;
-    if (T.sp == 0) { T.cur = RTOW_TRAV_DONE; return; }
-    --T.sp;
-    if (st.dist(T.sp) <= T.bestc * 1.000001f) T.cur = st.node(T.sp);
+    const float ub = T.bestc * 1.000001f;
+    int sp = T.sp, c = RTOW_TRAV_DONE;
+    while (sp > 0) {
+        const uint2 e = st.get(--sp);
+        if (__uint_as_float(e.y) <= ub) { c = (int)e.x; break; }
+    }
+    T.sp = sp; T.cur = c;
 }
 __device__ __forceinline__ bool fast_at_node(const FastTrav &T) { return T.cur >= 0; }
 __device__ __forceinline__ bool fast_at_leaf(const FastTrav &T) { return T.cur < 0 && T.cur != RTOW_TRAV_DONE && T.cur != RTOW_TRAV_POP; }
@@ -175,6 +181,7 @@ __device__ __forceinline__ void fast_node(const DScene &S, FastTrav &T, STACK &s
     const bool sx = T.ix < 0.f, sy = T.iy < 0.f, sz = T.iz < 0.f;
     const unsigned lox = __float_as_uint(q1.x), loy = __float_as_uint(q1.y), loz = __float_as_uint(q1.z);
     const unsigned hix = __float_as_uint(q1.w), hiy = __float_as_uint(q2.x), hiz = __float_as_uint(q2.y);
+    const unsigned bias = __float_as_uint(q2.z);     // FAST_NODE_BIAS_WORD
     const unsigned wnx = sx ? hix : lox, wfx = sx ? lox : hix;     // near / far plane bytes of the 4 children
     const unsigned wny = sy ? hiy : loy, wfy = sy ? loy : hiy;
     const unsigned wnz = sz ? hiz : loz, wfz = sz ? loz : hiz;
@@ -185,8 +192,8 @@ __device__ __forceinline__ void fast_node(const DScene &S, FastTrav &T, STACK &s
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         // plane distances of the (decoded) child box
-        const float nxk = fmaf(byte_f(wnx, k), ax, bx), nyk = fmaf(byte_f(wny, k), ay, by), nzk = fmaf(byte_f(wnz, k), az, bz);
-        const float fxk = fmaf(byte_f(wfx, k), ax, bx), fyk = fmaf(byte_f(wfy, k), ay, by), fzk = fmaf(byte_f(wfz, k), az, bz);
+        const float nxk = fmaf(byte_f(wnx, bias, k), ax, bx), nyk = fmaf(byte_f(wny, bias, k), ay, by), nzk = fmaf(byte_f(wnz, bias, k), az, bz);
+        const float fxk = fmaf(byte_f(wfx, bias, k), ax, bx), fyk = fmaf(byte_f(wfy, bias, k), ay, by), fzk = fmaf(byte_f(wfz, bias, k), az, bz);
         // exit distance under the ray's current slack bounds every accepted t in this child -> the child's own slack
         const float tf0 = fminf(fminf(fmaf(T.eta, aix, fxk), fmaf(T.eta, aiy, fyk)), fminf(fmaf(T.eta, aiz, fzk), ub));
         const float ek = fminf(T.eta, fmaf(T.Kd, fmaxf(tf0, 0.f) * 1.000001f, T.base));
@@ -276,7 +283,7 @@ __device__ __forceinline__ bool closest_hit_fast(const DScene &S, const Ray &r, 
     key.seed = g ? ((uint64_t)g->k1 << 32 | g->k0) : 0; key.pixel = g ? g->pixel : 0; key.sample = g ? g->sample : 0; key.bounce = g ? g->bounce : 0;
     fast_begin(S, r, tmin, tmax, T);
     while (T.cur != RTOW_TRAV_DONE) {
-        fast_pop_one(T, st);
+        fast_pop(T, st);
         if (fast_at_node(T)) fast_node<COUNT>(S, T, st, node_visits);
         else if (fast_at_leaf(T)) fast_leaf<COUNT>(S, T, key, prim_tests);
     }

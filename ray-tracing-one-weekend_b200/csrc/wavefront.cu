@@ -116,14 +116,12 @@ __global__ void __launch_bounds__(256) wf_generate_kernel(WavefrontLaunch W, rto
 
 // ---- extend ------------------------------------------------------------------------------------------------
 template <int MINB>
-__global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, WavefrontLaunch W, int parity, int refill_below, int leaf_min, int pop_tries) {
+__global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, WavefrontLaunch W, int parity, int refill_below, int leaf_min) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    __shared__ int s_ref[RTOW_WF_STACK_SMEM * 128];
-    __shared__ float s_d[RTOW_WF_STACK_SMEM * 128];
+    __shared__ uint2 s_stack[RTOW_WF_STACK_SMEM * 128];
     SmemStack<RTOW_WF_STACK_SMEM> st;
-    st.sref = s_ref + (threadIdx.x >> 5) * (RTOW_WF_STACK_SMEM * 32) + lane;
-    st.sd = s_d + (threadIdx.x >> 5) * (RTOW_WF_STACK_SMEM * 32) + lane;
+    st.col = s_stack + (threadIdx.x >> 5) * (RTOW_WF_STACK_SMEM * 32) + lane;
     FastTrav T;
     T.cur = RTOW_TRAV_DONE; T.sp = 0;
     int slot = 0;
@@ -195,7 +193,7 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
         if (!__any_sync(full, has_ray)) { if (!more) break; else continue; }
         // 3. vote-scheduled traversal rounds (see trace_persistent_kernel)
         for (;;) {
-            for (int a = 0; a < pop_tries; ++a) fast_pop_one(T, st);
+            fast_pop(T, st);
             const bool at_node = fast_at_node(T), at_leaf = fast_at_leaf(T);
             const unsigned mn = __ballot_sync(full, at_node), ml = __ballot_sync(full, at_leaf);
             const unsigned alive = __ballot_sync(full, T.cur != RTOW_TRAV_DONE);
@@ -333,7 +331,6 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
     static const int refill_env = [] { const char *e = getenv("RTOW_WF_REFILL"); return e ? atoi(e) : -1; }();
     const int refill = refill_env >= 0 ? refill_env : (S.fast_n_nodes >= 4096 ? 28 : 1);
     static const int leaf_min = [] { const char *e = getenv("RTOW_TRACE_LEAFMIN"); return e ? atoi(e) : 8; }();
-    static const int pops = [] { const char *e = getenv("RTOW_TRACE_POPS"); return e ? atoi(e) : 1; }();
     int dev = 0, sms = 148, per_sm = 4;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -363,8 +360,8 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
     for (long long it = 0;; ++it) {
         const bool sampled = prof && ((it & 7) == 6 || W.total_items <= (unsigned long long)W.pool);   // timed just before a sync point
         if (sampled) cudaEventRecord(ev[0], stream);
-        if (minb >= 8) wf_extend_kernel<8><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, pops);
-        else wf_extend_kernel<5><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, pops);
+        if (minb >= 8) wf_extend_kernel<8><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min);
+        else wf_extend_kernel<5><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min);
         if (sampled) cudaEventRecord(ev[1], stream);
         wf_shade_kernel<<<pool_blocks, 256, 0, stream>>>(S, W, cam, parity);
         if (sampled) cudaEventRecord(ev[2], stream);
