@@ -22,7 +22,8 @@ class RtowError(RuntimeError):
 
 
 def lib_path():
-    return os.path.join(_HERE, "csrc", "librtow_b200.so")
+    # RTOW_B200_LIB: an alternative build of the same library (kernel experiments, tools/build_variant.sh)
+    return os.environ.get("RTOW_B200_LIB") or os.path.join(_HERE, "csrc", "librtow_b200.so")
 
 
 def lib():

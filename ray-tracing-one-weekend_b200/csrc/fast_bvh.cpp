@@ -210,8 +210,9 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
         if (nd.right < 0 && nd.right != nd.left) { if (owner[~nd.right] >= 0) return fail("object referenced by two nodes"); owner[~nd.right] = i; }
         if (nd.left < 0 && nd.right == nd.left) twice[~nd.left] = 1;
     }
-    if (n > FAST_LEAF_ID_MASK) return fail("too many objects for the leaf reference encoding");
-    out.spheres.assign((size_t)n, make_float4(0, 0, 0, 0));
+    if (n >= FAST_LEAF_ID_MASK) return fail("too many objects for the leaf reference encoding");
+    out.spheres.assign((size_t)n + 1, make_float4(0, 0, 0, 0));
+    out.spheres[n] = make_float4(0, 0, 0, std::nanf(""));   // the never-hit sphere behind unused child slots (NaN discriminant)
     out.guards.assign((size_t)n * 2, make_float4(0, 0, 0, 0));
     std::vector<int32_t> leaf_ref(n);
     for (int o = 0; o < n; ++o) {
@@ -337,10 +338,13 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
             }
         }
         float4 *nd = &out.nodes[id * FAST_NODE_F4];
-        nd[0] = make_float4(p[0], p[1], p[2], i2f((int32_t)(ebyte[0] | ebyte[1] << 8 | ebyte[2] << 16)));
+        // cell sizes 2^e as float patterns ebyte << 23: x and y as upper halves packed in one word, z whole
+        nd[0] = make_float4(p[0], p[1], p[2], i2f((int32_t)((ebyte[0] << 23) | (ebyte[1] << 7))));
         nd[1] = make_float4(i2f((int32_t)qlo[0]), i2f((int32_t)qlo[1]), i2f((int32_t)qlo[2]), i2f((int32_t)qhi[0]));
-        nd[2] = make_float4(i2f((int32_t)qhi[1]), i2f((int32_t)qhi[2]), i2f((int32_t)FAST_NODE_BIAS_WORD), 0.f);
-        nd[3] = make_float4(i2f(w.ref[0]), i2f(w.ref[1]), i2f(w.ref[2]), i2f(w.ref[3]));
+        nd[2] = make_float4(i2f((int32_t)qhi[1]), i2f((int32_t)qhi[2]), i2f((int32_t)FAST_NODE_BIAS_WORD), i2f((int32_t)(ebyte[2] << 23)));
+        int32_t ref[4];
+        for (int k = 0; k < 4; ++k) ref[k] = w.ref[k] == FAST_EMPTY ? ~(int32_t)(FAST_LEAF_SPHERE | n) : w.ref[k];
+        nd[3] = make_float4(i2f(ref[0]), i2f(ref[1]), i2f(ref[2]), i2f(ref[3]));
     }
     return true;
 }

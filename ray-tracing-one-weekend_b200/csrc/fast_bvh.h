@@ -24,15 +24,17 @@ namespace rtow {
 // per-node grid (after Ylitie, Karras, Laine 2017 "Efficient incoherent ray traversal on GPUs through compressed wide
 // BVHs"): a lane that is alone on its node pays one L1 wavefront per load instruction, so bytes per node are what the
 // closest-hit kernel is bound by.  Decoded boxes contain the float boxes (lo rounded down, hi up): culling only.
-//   [0] origin p.xyz (float), exponent bytes ex | ey << 8 | ez << 16 (biased: cell size = 2^(e-127))
+//   [0] origin p.xyz (float), cell sizes of x and y: upper halves of the float patterns of 2^ex, 2^ey in one word
 //   [1] lo.x, lo.y, lo.z, hi.x   each word = the 4 children's bytes (child k in bits 8k..8k+7)
-//   [2] hi.y, hi.z, FAST_NODE_BIAS_WORD (the byte decoder's 2^15 float pattern, see rt_fast.cuh byte_f), -
-//   [3] child refs as int bits: >= 0 node index; < 0 leaf, ~ref = object id | FAST_LEAF_* flags; FAST_EMPTY = no child
+//   [2] hi.y, hi.z, FAST_NODE_BIAS_WORD (the byte decoder's 2^15 float pattern, see rt_fast.cuh byte_f), cell size of z (float)
+//   [3] child refs as int bits: >= 0 node index; < 0 leaf, ~ref = object id | FAST_LEAF_* flags.  An unused slot has an
+//       inverted byte interval (255..0) and refers to the never-hit sphere spheres[n_objects] (NaN radius), so the
+//       kernel needs no test for it
 // Per object (leaf), indexed by object id:
-//   spheres[obj]        {cx,cy,cz,r} of a bare Sphere leaf (FAST_LEAF_SPHERE), else zeros
+//   spheres[obj]        {cx,cy,cz,r} of a bare Sphere leaf (FAST_LEAF_SPHERE), else zeros; one extra never-hit entry
 //   guards[2*obj..+1]   {bmin.xyz, -} {bmax.xyz, -}: box of the reference BvhNode that owns the leaf
 enum { FAST_NODE_F4 = 4 };
-static const int32_t FAST_EMPTY = 0x7fffffff;
+static const int32_t FAST_EMPTY = 0x7fffffff;   // builder-internal marker of an unused slot
 static const uint32_t FAST_NODE_BIAS_WORD = 0x47000000u;
 enum {
     FAST_LEAF_SPHERE = 1 << 30,   // the object is one untransformed Sphere: test spheres[obj] directly

@@ -173,10 +173,10 @@ __device__ __forceinline__ void fast_node(const DScene &S, FastTrav &T, STACK &s
     const float4 *nd = S.fast_nodes + (size_t)T.cur * FAST_NODE_F4;
     float4 q0, q1, q2, q3;
     ldg256(nd, q0, q1); ldg256(nd + 2, q2, q3);
+    // plane t = q * (cell * 1/d) + (p - o) * 1/d, per axis; the cell sizes are powers of two: x and y as the upper
+    // halves of their float patterns in one word, z as a float
     const unsigned ex = __float_as_uint(q0.w);
-    // plane t = q * (cell * 1/d) + (p - o) * 1/d, per axis
-    const float ax = __uint_as_float((ex & 0xffu) << 23) * T.ix, ay = __uint_as_float((ex & 0xff00u) << 15) * T.iy,
-                az = __uint_as_float((ex & 0xff0000u) << 7) * T.iz;
+    const float ax = __uint_as_float(ex & 0xffff0000u) * T.ix, ay = __uint_as_float(ex << 16) * T.iy, az = q2.w * T.iz;
     const float bx = fmaf(q0.x, T.ix, -T.pox), by = fmaf(q0.y, T.iy, -T.poy), bz = fmaf(q0.z, T.iz, -T.poz);
     const bool sx = T.ix < 0.f, sy = T.iy < 0.f, sz = T.iz < 0.f;
     const unsigned lox = __float_as_uint(q1.x), loy = __float_as_uint(q1.y), loz = __float_as_uint(q1.z);
@@ -195,12 +195,14 @@ __device__ __forceinline__ void fast_node(const DScene &S, FastTrav &T, STACK &s
         const float nxk = fmaf(byte_f(wnx, bias, k), ax, bx), nyk = fmaf(byte_f(wny, bias, k), ay, by), nzk = fmaf(byte_f(wnz, bias, k), az, bz);
         const float fxk = fmaf(byte_f(wfx, bias, k), ax, bx), fyk = fmaf(byte_f(wfy, bias, k), ay, by), fzk = fmaf(byte_f(wfz, bias, k), az, bz);
         // exit distance under the ray's current slack bounds every accepted t in this child -> the child's own slack
-        const float tf0 = fminf(fminf(fmaf(T.eta, aix, fxk), fmaf(T.eta, aiy, fyk)), fminf(fmaf(T.eta, aiz, fzk), ub));
-        const float ek = fminf(T.eta, fmaf(T.Kd, fmaxf(tf0, 0.f) * 1.000001f, T.base));
+        // (no min with ub: T.eta already is <= Kd * bestc + base; no max with 0: a child whose exit lies behind the
+        // ray holds no hit and whatever slack it gets can only make it cull or cost a wasted visit)
+        const float tf0 = fminf(fminf(fmaf(T.eta, aix, fxk), fmaf(T.eta, aiy, fyk)), fmaf(T.eta, aiz, fzk));
+        const float ek = fminf(T.eta, fmaf(T.Kd, tf0 * 1.000001f, T.base));
         const float tn = fmaxf(fmaxf(fmaf(-ek, aix, nxk), fmaf(-ek, aiy, nyk)), fmaxf(fmaf(-ek, aiz, nzk), T.tmin));
         const float tf = fminf(fminf(fmaf(ek, aix, fxk), fmaf(ek, aiy, fyk)), fminf(fmaf(ek, aiz, fzk), ub));
         ref[k] = __float_as_int(lane4(q3, k));
-        d[k] = (tn <= tf && ref[k] != FAST_EMPTY) ? tn : inf;
+        d[k] = tn <= tf ? tn : inf;      // unused slots: inverted byte interval, and their ref is a never-hit leaf
     }
     // sort ascending by entry distance (5-comparator network)
 #define RTOW_CSWAP(a, b)                                                                     \

@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
             fast_pop(T, st);
             const bool at_node = fast_at_node(T), at_leaf = fast_at_leaf(T);
             const unsigned mn = __ballot_sync(full, at_node), ml = __ballot_sync(full, at_leaf);
-            const unsigned alive = __ballot_sync(full, T.cur != RTOW_TRAV_DONE);
+            const unsigned alive = mn | ml;        // after the pop a lane is at a node, at a leaf or done
             if (alive == 0 || (more && __popc(alive) < refill_below)) break;
             unsigned nv = 0, pt = 0;
             if (ml == 0 || (mn != 0 && __popc(ml) < leaf_min)) {
