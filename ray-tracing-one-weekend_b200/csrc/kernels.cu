@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, c
     const int lane = threadIdx.x & 31;
     __shared__ uint2 s_stack[RTOW_TRACE_STACK_SMEM * 128];
     SmemStack<RTOW_TRACE_STACK_SMEM> st;
-    st.col = s_stack + (threadIdx.x >> 5) * (RTOW_TRACE_STACK_SMEM * 32) + lane;
+    st.init(s_stack);
     FastTrav T;
     T.cur = RTOW_TRAV_DONE; T.sp = 0;
     uint64_t idx = 0;

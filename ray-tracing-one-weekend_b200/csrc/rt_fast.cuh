@@ -109,7 +109,13 @@ __device__ __forceinline__ void fast_begin(const DScene &S, const Ray &r, float 
 struct LocalStack {
     uint2 e[RTOW_FAST_STACK];
     __device__ __forceinline__ void put(int i, int r, float dist) { e[i] = make_uint2((unsigned)r, __float_as_uint(dist)); }
-    __device__ __forceinline__ uint2 get(int i) const { return e[i]; }
+    __device__ __forceinline__ int pop(int &sp, float ub) const {
+        while (sp > 0) {
+            const uint2 v = e[--sp];
+            if (__uint_as_float(v.y) <= ub) return (int)v.x;
+        }
+        return RTOW_TRAV_DONE;
+    }
     // entries 1..3 of a sorted child list (d1 <= d2 <= d3, culled ones = +inf), pushed far-to-near
     __device__ __forceinline__ int push3(int sp, const int *r, const float *dd) {
         const float inf = __int_as_float(0x7f800000);
@@ -119,32 +125,67 @@ struct LocalStack {
         return sp;
     }
 };
+// Shared-memory accesses by 32-bit shared address: one LDS/STS with an immediate offset, where indexing a __shared__
+// array makes the compiler re-derive the shared window base (four uniform-datapath instructions) at every access.
+__device__ __forceinline__ uint2 lds64(unsigned a) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts64(unsigned a, unsigned x, unsigned y) {
+    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(a), "r"(x), "r"(y) : "memory");
+}
 template <int CAP>
 struct SmemStack {
-    uint2 *col;     // this lane's column: entry i at col[i * 32]
+    unsigned col;   // shared address of this lane's column: entry i at col + i * 256
     uint2 loc[RTOW_FAST_STACK - CAP];
-    __device__ __forceinline__ void put(int i, int r, float dist) {
-        const uint2 v = make_uint2((unsigned)r, __float_as_uint(dist));
-        if (i < CAP) col[i * 32] = v; else loc[i - CAP] = v;
+    __device__ __forceinline__ void init(uint2 *block_stack) {
+        col = (unsigned)__cvta_generic_to_shared(block_stack + (threadIdx.x >> 5) * (CAP * 32) + (threadIdx.x & 31));
     }
-    __device__ __forceinline__ uint2 get(int i) const { return i < CAP ? col[i * 32] : loc[i - CAP]; }
+    __device__ __forceinline__ void put(int i, int r, float dist) {
+        if (i < CAP) sts64(col + i * 256, (unsigned)r, __float_as_uint(dist)); else loc[i - CAP] = make_uint2((unsigned)r, __float_as_uint(dist));
+    }
     // Branch-free in the common case (all three slots in shared memory): every candidate is stored, and the slot index
     // only advances past the live ones -- a culled entry (they sort last) is overwritten by the next store.
     __device__ __forceinline__ int push3(int sp, const int *r, const float *dd) {
         const float inf = __int_as_float(0x7f800000);
         if (sp + 3 <= CAP) {
-            uint2 *p = col + sp * 32;
-            p[0] = make_uint2((unsigned)r[3], __float_as_uint(dd[3]));
-            int k = dd[3] < inf ? 32 : 0;
-            p[k] = make_uint2((unsigned)r[2], __float_as_uint(dd[2]));
-            k += dd[2] < inf ? 32 : 0;
-            p[k] = make_uint2((unsigned)r[1], __float_as_uint(dd[1]));
-            return sp + (k >> 5) + (dd[1] < inf ? 1 : 0);
+            unsigned p = col + sp * 256;
+            sts64(p, (unsigned)r[3], __float_as_uint(dd[3]));
+            p += dd[3] < inf ? 256 : 0;
+            sts64(p, (unsigned)r[2], __float_as_uint(dd[2]));
+            p += dd[2] < inf ? 256 : 0;
+            sts64(p, (unsigned)r[1], __float_as_uint(dd[1]));
+            p += dd[1] < inf ? 256 : 0;
+            return (int)((p - col) >> 8);
         }
         if (dd[3] < inf) put(sp++, r[3], dd[3]);
         if (dd[2] < inf) put(sp++, r[2], dd[2]);
         if (dd[1] < inf) put(sp++, r[1], dd[1]);
         return sp;
+    }
+    // The topmost entry with distance <= ub, or RTOW_TRAV_DONE; sp ends below it.  Entries are read two at a time (a
+    // ray that has found its hit skips tens of stale ones, and the loop is a chain of shared-memory latencies).
+    __device__ __forceinline__ int pop(int &sp_io, float ub) const {
+        int sp = sp_io;
+        while (sp > CAP) {                                  // deep part, rare
+            const uint2 e = loc[--sp - CAP];
+            if (__uint_as_float(e.y) <= ub) { sp_io = sp; return (int)e.x; }
+        }
+        unsigned a = col + sp * 256;
+        while (sp >= 2) {
+            const uint2 e1 = lds64(a - 256), e2 = lds64(a - 512);
+            if (__uint_as_float(e1.y) <= ub) { sp_io = sp - 1; return (int)e1.x; }
+            sp -= 2; a -= 512;
+            if (__uint_as_float(e2.y) <= ub) { sp_io = sp; return (int)e2.x; }
+        }
+        if (sp == 1) {
+            const uint2 e = lds64(a - 256);
+            sp_io = 0;
+            return __uint_as_float(e.y) <= ub ? (int)e.x : RTOW_TRAV_DONE;
+        }
+        sp_io = 0;
+        return RTOW_TRAV_DONE;
     }
 };
 
@@ -154,13 +195,7 @@ struct SmemStack {
 template <class STACK>
 __device__ __forceinline__ void fast_pop(FastTrav &T, const STACK &st) {
     if (T.cur != RTOW_TRAV_POP) return;
-    const float ub = T.bestc * 1.000001f;
-    int sp = T.sp, c = RTOW_TRAV_DONE;
-    while (sp > 0) {
-        const uint2 e = st.get(--sp);
-        if (__uint_as_float(e.y) <= ub) { c = (int)e.x; break; }
-    }
-    T.sp = sp; T.cur = c;
+    T.cur = st.pop(T.sp, T.bestc * 1.000001f);
 }
 __device__ __forceinline__ bool fast_at_node(const FastTrav &T) { return T.cur >= 0; }
 __device__ __forceinline__ bool fast_at_leaf(const FastTrav &T) { return T.cur < 0 && T.cur != RTOW_TRAV_DONE && T.cur != RTOW_TRAV_POP; }

@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
     const int lane = threadIdx.x & 31;
     __shared__ uint2 s_stack[RTOW_WF_STACK_SMEM * 128];
     SmemStack<RTOW_WF_STACK_SMEM> st;
-    st.col = s_stack + (threadIdx.x >> 5) * (RTOW_WF_STACK_SMEM * 32) + lane;
+    st.init(s_stack);
     FastTrav T;
     T.cur = RTOW_TRAV_DONE; T.sp = 0;
     int slot = 0;
