@@ -399,7 +399,7 @@ def bvh_hit_bench(pkg, abi, torch, dev_t, stream, args):
             out[f"{name}_{tag}_mrays_per_s"] = len(rays) / (ms * 1e-3) / 1e6
         hits = d_hits.cpu().numpy().view(abi.hit_dtype).reshape(-1)
         out[f"{name}_hit_fraction"] = float((hits["prim_id"] >= 0).mean())
-        nv, pt = scene.trace_counters(rays[: 1 << 18], traverse=abi.TRAVERSE_FAST)
+        nv, pt = scene.trace_counters(rays[:: len(rays) >> 18], traverse=abi.TRAVERSE_FAST)    # every 64th ray: the whole frustum, not its first rows
         out[f"{name}_fast_node_visits_per_ray"], out[f"{name}_fast_prim_tests_per_ray"] = nv, pt
         # fractions of the FP32-issue roofline: counted work of this traversal, and the BVH-quality-independent
         # floor of 2*log2(N) slab tests + 1 sphere test = 1104 lane-ops per ray
@@ -410,6 +410,27 @@ def bvh_hit_bench(pkg, abi, torch, dev_t, stream, args):
         out[f"{name}_fast_frac_fp32_issue_counted"] = rate * out[f"{name}_fast_counted_ops_per_ray"] / peak
         out[f"{name}_fast_frac_fp32_issue_floor1104"] = rate * 1104.0 / peak
     out["rays_per_class"] = {k: int(len(v)) for k, v in sets.items()}
+    # the reference's own BvhNode::hit on the same spheres and ray classes, on this box's host cores (bounded sample); the GPU
+    # hit records of the sampled rays are checked against it on the way (prim id exact, t to 1e-5 relative)
+    if not args.no_cpu:
+        from oracle import bindings as obind
+        if obind.have_ref():
+            threads = host_threads()
+            ref = obind.RefOracle()
+            t0 = time.perf_counter()
+            rsc = ref.scene("bvh_stress", seed=SCENE_SEED, n=n_spheres)
+            cpu = {"kind": "reference", "cores": threads, "reference_bvh_build_s": time.perf_counter() - t0,
+                   "sample": f"{1 << 15} rays of each class (every {len(sets['coherent']) >> 15}th ray), world->hit() on the reference-built BvhNode, {threads} host threads"}
+            for name, rays in sets.items():
+                sub = np.ascontiguousarray(rays[:: len(rays) >> 15])
+                ref_hits, secs = rsc.trace(sub, threads=threads)
+                cpu[f"{name}_mrays_per_s"] = len(sub) / max(secs, 1e-9) / 1e6
+                gpu_hits, _ = scene.trace(sub, traverse=abi.TRAVERSE_FAST)
+                same = bool(np.array_equal(gpu_hits["prim_id"], ref_hits["prim_id"]))
+                hit = ref_hits["prim_id"] >= 0
+                terr = float(np.max(np.abs(gpu_hits["t"][hit] - ref_hits["t"][hit]) / np.abs(ref_hits["t"][hit]))) if hit.any() else 0.0
+                cpu[f"{name}_gpu_matches_reference"] = same and terr <= 1e-5
+            out["cpu_reference"] = cpu
     return out
 
 

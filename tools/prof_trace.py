@@ -50,7 +50,7 @@ def main():
         z.record(stream)
         torch.cuda.synchronize()
         ms = a.elapsed_time(z) / args.reps
-        nv, pt = scene.trace_counters(rays[: 1 << 16], traverse=args.traverse)
+        nv, pt = scene.trace_counters(rays[:: max(1, len(rays) >> 16)], traverse=args.traverse)
         print(f"{name}: {len(rays)} rays, {ms:.3f} ms, {len(rays) / ms / 1e3:.1f} Mrays/s, node visits/ray {nv:.1f}, prim tests/ray {pt:.1f}", flush=True)
 
 
