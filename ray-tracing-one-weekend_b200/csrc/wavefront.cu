@@ -87,10 +87,21 @@ __device__ __forceinline__ bool wf_start_path(const WavefrontLaunch &W, const rt
 
 // Hands the next work items to the lanes with need == true (all 32 lanes must call).  A lane whose items run out
 // gets dead = true.  Padding items are skipped by asking again.
-__device__ __forceinline__ void wf_refill(const WavefrontLaunch &W, const rtow_camera &cam, bool need, int slot, bool &dead) {
+// The lanes of `pre_mask` (warp-uniform; each has need == true) were given items pre_base, pre_base+1, ... by an
+// atomic their lane 0 issued earlier, so that its round trip is over by now.
+__device__ __forceinline__ void wf_refill(const WavefrontLaunch &W, const rtow_camera &cam, bool need, int slot, bool &dead,
+                                          unsigned pre_mask = 0u, unsigned long long pre_base = 0ull) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     dead = false;
+    if (pre_mask) {
+        pre_base = __shfl_sync(full, pre_base, 0);
+        if ((pre_mask >> lane) & 1u) {
+            const unsigned long long item = pre_base + __popc(pre_mask & ((1u << lane) - 1u));
+            if (item >= W.total_items) { dead = true; need = false; }
+            else if (wf_start_path(W, cam, item, slot)) need = false;
+        }
+    }
     for (;;) {
         const unsigned m = __ballot_sync(full, need);
         if (m == 0) break;
@@ -223,12 +234,24 @@ __device__ __forceinline__ void wf_add_pixel(const WavefrontLaunch &W, int pixel
     }
 }
 
-__global__ void __launch_bounds__(256) wf_shade_kernel(DScene S, WavefrontLaunch W, rtow_camera cam, int parity) {
+__global__ void __launch_bounds__(256, 4) wf_shade_kernel(DScene S, WavefrontLaunch W, rtow_camera cam, int parity) {
     __shared__ PerlinSmem perlin;
+    __shared__ unsigned s_end[RTOW_WF_MAX_CLASSES];     // running totals of the class queue lengths
+    static_assert(RTOW_WF_MAX_CLASSES <= 32, "one warp scans the class counts");
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned *counts = W.counts + parity * RTOW_WF_MAX_CLASSES;
+    if (threadIdx.x < 32) {       // one load per class and a warp scan, instead of a chain of dependent loads in every thread
+        unsigned v = lane < RTOW_WF_MAX_CLASSES ? counts[lane] : 0u;
+        for (int o = 1; o < RTOW_WF_MAX_CLASSES; o <<= 1) {
+            const unsigned u = __shfl_up_sync(full, v, o);
+            if (lane >= o) v += u;
+        }
+        if (lane < RTOW_WF_MAX_CLASSES) s_end[lane] = v;
+    }
     perlin_stage(S, &perlin);
     __syncthreads();
 
-    const unsigned *counts = W.counts + parity * RTOW_WF_MAX_CLASSES;
     const unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j == 0) {
         // the extend launch of this bounce is complete: reset what the next one uses
@@ -237,16 +260,18 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DScene S, WavefrontLaunch
         for (int c = 0; c < RTOW_WF_MAX_CLASSES; ++c) other[c] = 0u;
     }
     // queues are consumed class after class: thread j -> (class, index)
+    int cls = 0;
+#pragma unroll
+    for (int c = 0; c < RTOW_WF_MAX_CLASSES - 1; ++c) cls += j >= s_end[c] ? 1 : 0;
+    const bool valid = j < s_end[RTOW_WF_MAX_CLASSES - 1];
+    // Class 0 holds the rays that hit nothing: those paths end for certain, so their lanes claim the next work items now
+    // and the atomic's round trip runs under the state loads instead of after the shading (it was 18 % of this kernel's
+    // stall samples).
+    const unsigned early = __ballot_sync(full, valid && cls == 0);
+    unsigned long long early_base = 0ull;
+    if (early && lane == 0) early_base = atomicAdd(W.next_item, (unsigned long long)__popc(early));
     int slot = -1;
-    {
-        unsigned off = 0;
-        for (int c = 0; c < RTOW_WF_MAX_CLASSES; ++c) {
-            const unsigned n = counts[c];
-            if (j >= off && j < off + n) { slot = W.queue[(size_t)c * W.pool + (j - off)]; break; }
-            off += n;
-        }
-    }
-    const bool valid = slot >= 0;
+    if (valid) slot = W.queue[(size_t)cls * W.pool + (j - (cls ? s_end[cls - 1] : 0u))];
     bool ended = false;
     int pixel = 0;
     float Lr[3] = {0.f, 0.f, 0.f};
@@ -312,7 +337,7 @@ __global__ void __launch_bounds__(256) wf_shade_kernel(DScene S, WavefrontLaunch
     }
     if (ended) wf_add_pixel(W, pixel, Lr);
     bool dead;
-    wf_refill(W, cam, ended, valid ? slot : 0, dead);
+    wf_refill(W, cam, ended, valid ? slot : 0, dead, early, early_base);
 }
 
 __global__ void wf_finalize_kernel(const unsigned long long *__restrict__ fixed, float *__restrict__ accum, size_t n, double inv_scale) {
