@@ -29,7 +29,12 @@ namespace rtow {
 
 // 256-bit global accesses (LDG.E.256 / STG.E.256); p must be 32-byte aligned
 __device__ __forceinline__ void ld256(const void *p, float4 &a, float4 &b) {
+#ifdef RTOW_STATE_L1_DEFAULT
     asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+#else
+    // the slot state streams through (100 MB per bounce): kept out of L1 so that the scene's few KB stay there
+    asm volatile("ld.global.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+#endif
                  : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
                  : "l"(p) : "memory");
 }
@@ -227,7 +232,8 @@ __device__ __forceinline__ void wf_add_pixel(const WavefrontLaunch &W, int pixel
     for (int k = 0; k < 3; ++k) {
         const float v = L[k];
         if (v != 0.f && fabsf(v) <= 1e9f) {    // NaN / inf / absurd radiance never reaches the sum (reference: undefined, main.cpp:963)
-            atomicAdd(&W.fixed[(size_t)(pixel - W.L.pixel_begin) * 3 + k], (unsigned long long)__double2ll_rn((double)v * WF_FIXED_SCALE));
+            // v * 2^32 is exact in fp32 (|v| <= 1e9 < 2^30), so the float conversion rounds the same real number the double one did
+            atomicAdd(&W.fixed[(size_t)(pixel - W.L.pixel_begin) * 3 + k], (unsigned long long)__float2ll_rn(v * (float)WF_FIXED_SCALE));
             if (W.fixed_sq && fabsf(v) <= 1e6f)
                 atomicAdd(&W.fixed_sq[(size_t)(pixel - W.L.pixel_begin) * 3 + k], (unsigned long long)__double2ll_rn((double)v * (double)v * WF_FIXED_SQ_SCALE));
         }
