@@ -75,7 +75,7 @@ struct FastTrav {
     Ray r;                      // in the root aggregate's space
     float tmin, tmax;
     // cull-side constants (FMA allowed: nothing here decides acceptance)
-    float ix, iy, iz, pox, poy, poz;
+    float ix, iy, iz;           // (o * 1/d is recomputed where used: a multiply on the idle FMA pipe is cheaper than a live register here)
     float Kd, base, eta_g;
     // running result
     float best, bestc, eta;
@@ -93,7 +93,6 @@ __device__ __forceinline__ void fast_begin(const DScene &S, const Ray &r, float 
     T.base = 3e-6f * S.scene_radius + 1e-6f * (omax + D);
     T.eta_g = 1.5e-3f * D + T.base;
     T.Kd = 1.5e-3f * dl;
-    T.pox = r.ox * T.ix; T.poy = r.oy * T.iy; T.poz = r.oz * T.iz;
     T.best = __int_as_float(0x7f800000);
     T.bestc = tmax;                 // cull bound: accepted hits have t < tmax and t <= best
     T.best_obj = -1; T.best_prim = -1;
@@ -212,7 +211,8 @@ __device__ __forceinline__ void fast_node(const DScene &S, FastTrav &T, STACK &s
     // halves of their float patterns in one word, z as a float
     const unsigned ex = __float_as_uint(q0.w);
     const float ax = __uint_as_float(ex & 0xffff0000u) * T.ix, ay = __uint_as_float(ex << 16) * T.iy, az = q2.w * T.iz;
-    const float bx = fmaf(q0.x, T.ix, -T.pox), by = fmaf(q0.y, T.iy, -T.poy), bz = fmaf(q0.z, T.iz, -T.poz);
+    const float pox = T.r.ox * T.ix, poy = T.r.oy * T.iy, poz = T.r.oz * T.iz;
+    const float bx = fmaf(q0.x, T.ix, -pox), by = fmaf(q0.y, T.iy, -poy), bz = fmaf(q0.z, T.iz, -poz);
     const bool sx = T.ix < 0.f, sy = T.iy < 0.f, sz = T.iz < 0.f;
     const unsigned lox = __float_as_uint(q1.x), loy = __float_as_uint(q1.y), loz = __float_as_uint(q1.z);
     const unsigned hix = __float_as_uint(q1.w), hiy = __float_as_uint(q2.x), hiz = __float_as_uint(q2.y);
@@ -264,9 +264,10 @@ struct RngKey {
 // t after every axis and the test returns true.  Almost every candidate passes here; the rest (hits within the margin
 // of a guard face) take the reference's division-form test (6 IEEE divisions) as before.
 __device__ __forceinline__ bool guard_surely_passes(const float4 &g0, const float4 &g1, const FastTrav &T, float t) {
-    const float ax0 = fmaf(g0.x, T.ix, -T.pox), ax1 = fmaf(g1.x, T.ix, -T.pox);
-    const float ay0 = fmaf(g0.y, T.iy, -T.poy), ay1 = fmaf(g1.y, T.iy, -T.poy);
-    const float az0 = fmaf(g0.z, T.iz, -T.poz), az1 = fmaf(g1.z, T.iz, -T.poz);
+    const float pox = T.r.ox * T.ix, poy = T.r.oy * T.iy, poz = T.r.oz * T.iz;
+    const float ax0 = fmaf(g0.x, T.ix, -pox), ax1 = fmaf(g1.x, T.ix, -pox);
+    const float ay0 = fmaf(g0.y, T.iy, -poy), ay1 = fmaf(g1.y, T.iy, -poy);
+    const float az0 = fmaf(g0.z, T.iz, -poz), az1 = fmaf(g1.z, T.iz, -poz);
     const float lo = fmaxf(fmaxf(fminf(ax0, ax1), fminf(ay0, ay1)), fmaxf(fminf(az0, az1), T.tmin));
     const float hi = fminf(fminf(fmaxf(ax0, ax1), fmaxf(ay0, ay1)), fminf(fmaxf(az0, az1), T.tmax));
     const float m = 1e-5f * fabsf(t) + T.base * fmaxf(fmaxf(fabsf(T.ix), fabsf(T.iy)), fabsf(T.iz));
