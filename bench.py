@@ -185,6 +185,7 @@ def run_product(args):
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path")
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # stdout carries the one JSON line only (NCCL's version banner goes there otherwise)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev_t = torch.device("cuda", local)
     stream = torch.cuda.current_stream()
