@@ -210,7 +210,6 @@ int ensure_wavefront(rtow_scene *s, int pool, size_t pixels) {
     auto grab = [&](void **p, size_t bytes) { cudaError_t e = cudaMalloc(p, bytes); if (e == cudaSuccess) s->wf_allocs.push_back(*p); return e; };
     WavefrontLaunch &W = s->wf;
     CUDA_TRY(grab((void **)&W.ray, (size_t)pool * 32));
-    CUDA_TRY(grab((void **)&W.tl, (size_t)pool * 32));
     CUDA_TRY(grab((void **)&W.idh, (size_t)pool * 32));
     CUDA_TRY(grab((void **)&W.queue, (size_t)pool * RTOW_WF_MAX_CLASSES * 4));
     CUDA_TRY(grab((void **)&W.counts, 2 * RTOW_WF_MAX_CLASSES * 4));

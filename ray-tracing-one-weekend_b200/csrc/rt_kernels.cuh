@@ -35,13 +35,12 @@ struct WavefrontLaunch {
     RenderLaunch L;
     int pool;                             // path slots (multiple of 256)
     unsigned long long total_items;       // work items = pixel groups of 32 x samples (incl. padding pixels)
-    // per-slot state (SoA in HBM)
-    // three arrays of 32-byte elements (two 16-byte halves each), so that the shade kernel -- which reaches its slot
-    // through a queue, one scattered line per lane -- moves a slot with three 256-bit loads and stores instead of six
-    float4 *ray;                          // [2*slot] {o.xyz, time}  [2*slot+1] {d.xyz, -}
-    float4 *tl;                           // [2*slot] path throughput T  [2*slot+1] radiance so far L
+    // per-slot state (SoA in HBM): two arrays of 32-byte elements (two 16-byte halves each), so that the shade kernel --
+    // which reaches its slot through a queue, one scattered line per lane -- moves a slot with two 256-bit loads and stores.
+    // 64 bytes per path, no padding: the throughput T sits in the three words the ray and the ids leave free.
+    float4 *ray;                          // [2*slot] {o.xyz, time}  [2*slot+1] {d.xyz, T.x}
     int4 *idh;                            // [2*slot] {pixel, sample, next Philox draw, depth}; depth < 0: the slot is dead
-                                          // [2*slot+1] {t bits, prim id (< 0: miss), -, -} written by the extend kernel
+                                          // [2*slot+1] {t bits, prim id (< 0: miss)} written by the extend kernel, {T.y, T.z}
     int *queue;                           // RTOW_WF_MAX_CLASSES x pool slot indices, by shading class
     unsigned *counts;                     // 2 x RTOW_WF_MAX_CLASSES queue lengths (double-buffered by bounce parity)
     unsigned long long *fixed;            // W*H*3 radiance sums, Q31.32

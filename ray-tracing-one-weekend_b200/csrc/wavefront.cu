@@ -84,9 +84,9 @@ __device__ __forceinline__ bool wf_start_path(const WavefrontLaunch &W, const rt
     float v = (float)((double)row + (double)jv) / (float)W.L.height;
     Ray r;
     camera_ray(cam, u, v, g, r);
-    st256(W.ray + 2 * (size_t)slot, make_float4(r.ox, r.oy, r.oz, r.time), make_float4(r.dx, r.dy, r.dz, 0.f));
-    st256(W.tl + 2 * (size_t)slot, make_float4(1.f, 1.f, 1.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f));
-    W.idh[2 * (size_t)slot] = make_int4(pixel, W.L.sample_begin + s, (int)g.next, 0);
+    st256(W.ray + 2 * (size_t)slot, make_float4(r.ox, r.oy, r.oz, r.time), make_float4(r.dx, r.dy, r.dz, 1.f));
+    st256(W.idh + 2 * (size_t)slot, make_float4(__int_as_float(pixel), __int_as_float(W.L.sample_begin + s), __int_as_float((int)g.next), __int_as_float(0)),
+          make_float4(0.f, __int_as_float(-1), 1.f, 1.f));
     return true;
 }
 
@@ -282,14 +282,15 @@ __global__ void __launch_bounds__(256, 4) wf_shade_kernel(DScene S, WavefrontLau
     int pixel = 0;
     float Lr[3] = {0.f, 0.f, 0.f};
     if (valid) {
-        float4 a, b, t4, l4, idf, hf;
+        float4 a, b, idf, hf;
         ld256(W.ray + 2 * (size_t)slot, a, b);
-        ld256(W.tl + 2 * (size_t)slot, t4, l4);
         ld256(W.idh + 2 * (size_t)slot, idf, hf);
         const int4 id = make_int4(__float_as_int(idf.x), __float_as_int(idf.y), __float_as_int(idf.z), __float_as_int(idf.w));
         const float2 hr = make_float2(hf.x, hf.y);
-        float T[3] = {t4.x, t4.y, t4.z};
-        Lr[0] = l4.x; Lr[1] = l4.y; Lr[2] = l4.z;
+        // The path's throughput T rides in the three spare words of the two state elements.  Its radiance so far needs no
+        // storage: only DiffuseLight emits and it never scatters (material.h:124-137), and a miss ends the path, so radiance
+        // is only ever added at a path's last vertex.
+        float T[3] = {b.w, hf.z, hf.w};
         pixel = id.x;
         int depth = id.w;
         Ray r;
@@ -326,9 +327,12 @@ __global__ void __launch_bounds__(256, 4) wf_shade_kernel(DScene S, WavefrontLau
                 Lr[0] += T[0] * em[0]; Lr[1] += T[1] * em[1]; Lr[2] += T[2] * em[2];
                 if (go) {
                     T[0] *= atten[0]; T[1] *= atten[1]; T[2] *= atten[2];
-                    st256(W.ray + 2 * (size_t)slot, make_float4(h.p[0], h.p[1], h.p[2], stime), make_float4(sd[0], sd[1], sd[2], 0.f));
-                    st256(W.tl + 2 * (size_t)slot, make_float4(T[0], T[1], T[2], 0.f), make_float4(Lr[0], Lr[1], Lr[2], 0.f));
-                    W.idh[2 * (size_t)slot] = make_int4(id.x, id.y, (int)g.next, depth + 1);
+                    st256(W.ray + 2 * (size_t)slot, make_float4(h.p[0], h.p[1], h.p[2], stime), make_float4(sd[0], sd[1], sd[2], T[0]));
+                    st256(W.idh + 2 * (size_t)slot, make_float4(idf.x, idf.y, __int_as_float((int)g.next), __int_as_float(depth + 1)),
+                          make_float4(0.f, __int_as_float(-1), T[1], T[2]));
+                    // (a surface that both emits and scatters does not exist behind this API; if one ever did, its emission goes
+                    // to the pixel here instead of being carried)
+                    if (Lr[0] != 0.f || Lr[1] != 0.f || Lr[2] != 0.f) wf_add_pixel(W, pixel, Lr);
                 } else {
                     ended = true;
                 }
