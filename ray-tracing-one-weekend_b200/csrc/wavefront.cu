@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(256, 4) wf_shade_kernel(DScene S, WavefrontLau
         const int4 id = make_int4(__float_as_int(idf.x), __float_as_int(idf.y), __float_as_int(idf.z), __float_as_int(idf.w));
         const float2 hr = make_float2(hf.x, hf.y);
         // The path's throughput T rides in the three spare words of the two state elements.  Its radiance so far needs no
-        // storage: only DiffuseLight emits and it never scatters (material.h:124-137), and a miss ends the path, so radiance
+        // storage: only DiffuseLight emits and it never scatters (material.h:122-135), and a miss ends the path, so radiance
         // is only ever added at a path's last vertex.
         float T[3] = {b.w, hf.z, hf.w};
         pixel = id.x;

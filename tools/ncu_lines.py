@@ -3,7 +3,7 @@
 
   ncu -i prof.ncu-rep --page source --csv > src.csv
   cuobjdump -xelf all lib.so ; nvdisasm -g -c kernels.sm_100a.cubin > kernels.sass
-  python tools/ncu_lines.py src.csv kernels.sass <mangled-kernel-substring> [top_n]
+  python tools/ncu_lines.py src.csv kernels.sass <mangled-kernel-substring> [top_n] [launch index in the report, 1-based]
 
 Runs on the CPU box (no GPU needed)."""
 import collections
@@ -34,6 +34,7 @@ def load_lines(sass_path, kernel_sub):
 def main():
     src_csv, sass, kernel_sub = sys.argv[1:4]
     top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
+    want = int(sys.argv[5]) if len(sys.argv) > 5 else 1      # which captured launch of the report (1-based)
     lines = load_lines(sass, kernel_sub)
     rows = list(csv.reader(open(src_csv)))
     # the page holds one table per kernel instance: header row starts with "Address"
@@ -48,7 +49,7 @@ def main():
             hdr = {h: i for i, h in enumerate(r)}
             tables += 1
             continue
-        if hdr is None or tables > 1 or not r or not re.match(r"^(0x)?[0-9a-f]+$", r[0]):
+        if hdr is None or tables != want or not r or not re.match(r"^(0x)?[0-9a-f]+$", r[0]):
             continue
         addr = int(r[0], 16)
         if first_addr is None:
