@@ -98,8 +98,7 @@ __global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, c
     bool has_ray = false;
     bool more = true;             // the queue may still hold rays
     unsigned nv = 0, pt = 0;
-    RngKey key;
-    key.seed = seed; key.pixel = key.sample = key.bounce = 0;
+    const auto key_of = [&] { RngKey k; k.seed = seed; k.pixel = (uint32_t)idx; k.sample = (uint32_t)(idx >> 32); k.bounce = 0; return k; };
 
     for (;;) {
         // 1. finished lanes park their result
@@ -126,7 +125,6 @@ __global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, c
                     r.dx = __ldg(q + 3); r.dy = __ldg(q + 4); r.dz = __ldg(q + 5);
                     r.time = __ldg(q + 6);
                     const float tmin = __ldg(q + 7), tmax = __ldg(q + 8);
-                    key.pixel = (uint32_t)idx; key.sample = (uint32_t)(idx >> 32);
                     root_ray(S, r);
                     if (fast_covers(S, r, tmin, tmax)) {
                         fast_begin(S, r, tmin, tmax, T);
@@ -150,7 +148,7 @@ __global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, c
             if (ml == 0 || (mn != 0 && __popc(ml) < leaf_min)) {
                 if (at_node) fast_node<COUNT>(S, T, st, nv);
             } else {
-                if (at_leaf) fast_leaf<COUNT>(S, T, key, pt);
+                if (at_leaf) fast_leaf<COUNT>(S, T, key_of, pt);
             }
         }
     }

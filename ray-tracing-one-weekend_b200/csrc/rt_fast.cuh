@@ -274,8 +274,10 @@ __device__ __forceinline__ bool guard_surely_passes(const float4 &g0, const floa
     return lo + m < t && t < hi - m;     // false on NaN
 }
 
-template <bool COUNT>
-__device__ __forceinline__ void fast_leaf(const DScene &S, FastTrav &T, const RngKey &key, unsigned &prim_tests) {
+// `key_of()` returns the RngKey of the lane's ray.  It is only called when the leaf holds a medium (whose free-flight draw
+// needs the path's Philox counter), so the persistent kernels fetch the key then instead of keeping it in three registers.
+template <bool COUNT, class KEYFN>
+__device__ __forceinline__ void fast_leaf(const DScene &S, FastTrav &T, const KEYFN &key_of, unsigned &prim_tests) {
     const int code = ~T.cur;
     const int obj = code & FAST_LEAF_ID_MASK;
     float t = 0.f; int pid = -1; bool h;
@@ -284,6 +286,7 @@ __device__ __forceinline__ void fast_leaf(const DScene &S, FastTrav &T, const Rn
         const float4 sph = __ldg(S.fast_spheres + obj);
         h = sphere_t(sph.x, sph.y, sph.z, sph.w, T.r, T.tmin, T.tmax, t);
     } else {
+        const RngKey key = key_of();
         Rng g;
         rng_init(g, key.seed, key.pixel, key.sample);
         g.bounce = key.bounce;
@@ -323,7 +326,7 @@ __device__ __forceinline__ bool closest_hit_fast(const DScene &S, const Ray &r, 
     while (T.cur != RTOW_TRAV_DONE) {
         fast_pop(T, st);
         if (fast_at_node(T)) fast_node<COUNT>(S, T, st, node_visits);
-        else if (fast_at_leaf(T)) fast_leaf<COUNT>(S, T, key, prim_tests);
+        else if (fast_at_leaf(T)) fast_leaf<COUNT>(S, T, [&] { return key; }, prim_tests);
     }
     return fast_result(S, T, t_out, prim_out);
 }

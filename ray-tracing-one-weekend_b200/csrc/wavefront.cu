@@ -142,9 +142,13 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
     T.cur = RTOW_TRAV_DONE; T.sp = 0;
     int slot = 0;
     bool has_ray = false, more = true;
-    unsigned long long rays = 0;
-    RngKey key;
-    key.seed = W.L.seed; key.pixel = key.sample = key.bounce = 0;
+    unsigned rays = 0;
+    // the path's Philox key, read back from the slot when a medium asks for it (rare) instead of living in three registers
+    const auto key_of = [&] {
+        const int4 id = W.idh[2 * (size_t)slot];
+        RngKey k; k.seed = W.L.seed; k.pixel = (uint32_t)id.x; k.sample = (uint32_t)id.y; k.bounce = (uint32_t)id.w;
+        return k;
+    };
     unsigned *counts = W.counts + parity * RTOW_WF_MAX_CLASSES;
     const bool use_fast = W.L.traverse == RTOW_TRAVERSE_FAST && S.fast_nodes != nullptr;
 
@@ -188,15 +192,14 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
                         slot = (int)mine; has_ray = true; rays++;
                         Ray r;
                         r.ox = a.x; r.oy = a.y; r.oz = a.z; r.time = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z;
-                        key.pixel = (uint32_t)id.x; key.sample = (uint32_t)id.y; key.bounce = (uint32_t)id.w;
                         root_ray(S, r);
                         if (use_fast && fast_covers(S, r, 0.001f, FLT_MAX)) {
                             fast_begin(S, r, 0.001f, FLT_MAX, T);
                         } else {
                             // list scenes (nothing to cull) and rays outside the culling argument: the reference walk
                             Rng g;
-                            rng_init(g, key.seed, key.pixel, key.sample);
-                            g.bounce = key.bounce;
+                            rng_init(g, W.L.seed, (uint32_t)id.x, (uint32_t)id.y);
+                            g.bounce = (uint32_t)id.w;
                             float t; int pid; unsigned nv = 0, pt = 0;
                             T.best_obj = -1; T.best_prim = -1;
                             if (closest_hit_exact<false>(S, r, 0.001f, FLT_MAX, &g, t, pid, nv, pt)) { T.best = t; T.best_obj = 0; T.best_prim = pid; }
@@ -218,12 +221,12 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
             if (ml == 0 || (mn != 0 && __popc(ml) < leaf_min)) {
                 if (at_node) fast_node<false>(S, T, st, nv);
             } else {
-                if (at_leaf) fast_leaf<false>(S, T, key, pt);
+                if (at_leaf) fast_leaf<false>(S, T, key_of, pt);
             }
         }
     }
     for (int off = 16; off; off >>= 1) rays += __shfl_down_sync(full, rays, off);
-    if (lane == 0 && rays) atomicAdd(&W.stats[0], rays);
+    if (lane == 0 && rays) atomicAdd(&W.stats[0], (unsigned long long)rays);
 }
 
 // ---- shade -------------------------------------------------------------------------------------------------
