@@ -296,7 +296,9 @@ def run_product(args):
         shade_ms = prof.shade_ms_sum / prof.sampled_iterations
         trav_ops_per_ray = box_ops * wc.node_visits_per_ray + OPS_PRIM * wc.prim_tests_per_ray
         achieved_tops = prof.pool_slots * trav_ops_per_ray / (ext_ms * 1e-3) / 1e12
-        dom = {"kernel": "wf_extend_kernel", "kernel_ms": ext_ms, "launches_per_step": prof.iterations, "units_per_launch": prof.pool_slots,
+        # list scenes and EXACT traversal run the reference walk in its own kernel (wavefront.cu run_wavefront)
+        ext_name = "wf_extend_kernel" if wc.traverse == abi.TRAVERSE_FAST else "wf_extend_exact_kernel"
+        dom = {"kernel": ext_name, "kernel_ms": ext_ms, "launches_per_step": prof.iterations, "units_per_launch": prof.pool_slots,
                "ops_per_unit": trav_ops_per_ray, "share_of_step": ext_ms / (ext_ms + shade_ms), "shade_kernel_ms": shade_ms,
                "sampled_launches": prof.sampled_iterations}
         kernel_name = "wavefront"
@@ -315,11 +317,11 @@ def run_product(args):
     hbm_ach = alg_bytes / (kern_ms_last * 1e-3) / 1e9
     hbm_note = "accumulator read+write only: this kernel is not HBM-bound"
     traffic = None
-    if dom["kernel"] == "wf_extend_kernel":
+    if dom["kernel"].startswith("wf_extend"):
         # per launch and slot: ray 32 B + ids 16 B read, hit 8 B + queue entry 4 B written
         alg_bytes = prof.pool_slots * (32 + 16 + 8 + 4)
         hbm_ach = alg_bytes / (dom["kernel_ms"] * 1e-3) / 1e9
-        hbm_note = "wf_extend_kernel: slot state read + hit/queue written per launch; the pool is partly L2-resident and the kernel is issue-bound, not HBM-bound"
+        hbm_note = dom["kernel"] + ": slot state read + hit/queue written per launch; the pool is partly L2-resident and the kernel is issue-bound, not HBM-bound"
         try:      # measured DRAM bytes per launch of the same kernel on the same scene and pool (one ncu --set full capture)
             t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["wf_extend_kernel"]
             if (W, H, args.scene) == (WIDTH, HEIGHT, SCENE) and prof.pool_slots == 1 << 20:

@@ -229,6 +229,45 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
     if (lane == 0 && rays) atomicAdd(&W.stats[0], (unsigned long long)rays);
 }
 
+// ---- extend, reference walk -----------------------------------------------------------------------------------
+// List scenes (a HitableList world has nothing to cull) and EXACT traversal: every ray walks the reference structure as is
+// (hitableList.h:20-38 / bvhNode.h:66-96).  No traversal state to keep, so this is the plain form -- one slot per thread,
+// no shared-memory stack -- and the primitive code gets the registers (wf_extend_kernel at 64 registers spilled 750 bytes
+// of its unused FastTrav around every call).
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) wf_extend_exact_kernel(DScene S, WavefrontLaunch W, int parity) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const size_t slot = (size_t)blockIdx.x * blockDim.x + threadIdx.x;      // the grid covers the pool exactly (pool % 256 == 0)
+    unsigned *counts = W.counts + parity * RTOW_WF_MAX_CLASSES;
+    const int4 id = W.idh[2 * slot];
+    float4 a, b;
+    ld256(W.ray + 2 * slot, a, b);
+    int cls = -1;
+    if (id.w >= 0) {
+        Ray r;
+        r.ox = a.x; r.oy = a.y; r.oz = a.z; r.time = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z;
+        root_ray(S, r);
+        Rng g;
+        rng_init(g, W.L.seed, (uint32_t)id.x, (uint32_t)id.y);
+        g.bounce = (uint32_t)id.w;
+        float t = 0.f; int pid = -1; unsigned nv = 0, pt = 0;
+        if (!closest_hit_exact<false>(S, r, 0.001f, FLT_MAX, &g, t, pid, nv, pt)) { t = 0.f; pid = -1; }
+        *reinterpret_cast<float2 *>(W.idh + 2 * slot + 1) = make_float2(t, __int_as_float(pid));
+        cls = pid >= 0 ? __ldg(&S.materials[2 * __ldg(&S.prims[pid * 5]).y + 1]).w : 0;
+    }
+    const unsigned same = __match_any_sync(full, cls);
+    if (cls >= 0) {
+        const int leader = __ffs(same) - 1;
+        unsigned base = 0;
+        if (lane == leader) base = atomicAdd(&counts[cls], (unsigned)__popc(same));
+        base = __shfl_sync(same, base, leader);
+        W.queue[(size_t)cls * W.pool + base + __popc(same & ((1u << lane) - 1u))] = (int)slot;
+    }
+    const unsigned live = __ballot_sync(full, cls >= 0);
+    if (lane == 0 && live) atomicAdd(&W.stats[0], (unsigned long long)__popc(live));
+}
+
 // ---- shade -------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void wf_add_pixel(const WavefrontLaunch &W, int pixel, const float L[3]) {
 #pragma unroll
@@ -376,6 +415,9 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
     // walk, which is call-heavy rather than state-heavy: 8 blocks x 64 registers measured 6 % faster (smoke scene)
     static const int minb_env = [] { const char *e = getenv("RTOW_WF_MINB"); return e ? atoi(e) : 0; }();   // tuning knob
     const int minb = minb_env ? minb_env : (S.fast_nodes ? 5 : 8);
+    static const int exact_env = [] { const char *e = getenv("RTOW_WF_EXACT_KERNEL"); return e ? atoi(e) : 1; }();   // 0: A/B against wf_extend_kernel
+    static const int exact_minb = [] { const char *e = getenv("RTOW_WF_EXACT_MINB"); return e ? atoi(e) : 8; }();
+    const bool exact_walk = exact_env && !(W.L.traverse == RTOW_TRAVERSE_FAST && S.fast_nodes != nullptr);
     if (minb >= 8) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_extend_kernel<8>, 128, 0);
     else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_extend_kernel<5>, 128, 0);
     const unsigned ext_blocks = (unsigned)std::min<long long>((W.pool + 127) / 128, (long long)sms * std::max(per_sm, 1));
@@ -398,7 +440,10 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
     for (long long it = 0;; ++it) {
         const bool sampled = prof && ((it & 7) == 6 || W.total_items <= (unsigned long long)W.pool);   // timed just before a sync point
         if (sampled) cudaEventRecord(ev[0], stream);
-        if (minb >= 8) wf_extend_kernel<8><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min);
+        if (exact_walk && exact_minb >= 8) wf_extend_exact_kernel<8><<<(unsigned)(W.pool / 128), 128, 0, stream>>>(S, W, parity);
+        else if (exact_walk && exact_minb >= 6) wf_extend_exact_kernel<6><<<(unsigned)(W.pool / 128), 128, 0, stream>>>(S, W, parity);
+        else if (exact_walk) wf_extend_exact_kernel<5><<<(unsigned)(W.pool / 128), 128, 0, stream>>>(S, W, parity);
+        else if (minb >= 8) wf_extend_kernel<8><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min);
         else wf_extend_kernel<5><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min);
         if (sampled) cudaEventRecord(ev[1], stream);
         wf_shade_kernel<<<pool_blocks, 256, 0, stream>>>(S, W, cam, parity);
