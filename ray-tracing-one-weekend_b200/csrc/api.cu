@@ -366,6 +366,14 @@ int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out)
         mats[2 * i + 1] = make_int4(f[2], f[3], textured && texture_needs_uv(desc, m.tex_id) ? 1 : 0, class_of_key[key]);
     }
     if ((rc = upload(s, mats.data(), mats.size(), &D.materials))) return rc;
+    {   // shading class per primitive: one load where prims -> materials were two dependent ones at the end of every extend batch
+        std::vector<int32_t> pc((size_t)std::max(desc->n_prims, 1), 0);
+        for (int i = 0; i < desc->n_prims; ++i) {
+            const int m = desc->prims[i].mat_id;
+            pc[i] = (m >= 0 && m < desc->n_materials) ? mats[2 * (size_t)m + 1].w : 0;
+        }
+        if ((rc = upload(s, pc.data(), pc.size(), &D.prim_class))) return rc;
+    }
 
     std::vector<int4> texs((size_t)desc->n_textures * 2);
     for (int i = 0; i < desc->n_textures; ++i) {
@@ -421,6 +429,12 @@ int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out)
             D.scene_radius = fb.radius;
             D.fast_time_lo = fb.time_lo; D.fast_time_hi = fb.time_hi;
             if ((rc = upload(s, fb.nodes.data(), fb.nodes.size(), &D.fast_nodes))) return rc;
+            // the spare word of a leaf's guard box carries its single primitive's id (-1: a run of primitives), so that an
+            // accepted sphere hit has its primitive id without a further load
+            for (int o = 0; o < desc->n_objects; ++o) {
+                const int32_t single = objs[o].w;
+                std::memcpy(&fb.guards[2 * (size_t)o].w, &single, 4);
+            }
             if ((rc = upload(s, fb.spheres.data(), fb.spheres.size(), &D.fast_spheres))) return rc;
             if ((rc = upload(s, fb.guards.data(), fb.guards.size(), &D.fast_guards))) return rc;
             s->has_fast = true;

@@ -49,6 +49,7 @@ struct DScene {
     int32_t fast_n_nodes, fast_root;
     const float4 *fast_nodes;     // 8 x float4 per node (fast_bvh.h)
     const float4 *fast_spheres;   // per object: {c, r} of a bare Sphere leaf (fast_bvh.h)
+    const int *prim_class;        // shading class (wavefront queues) per primitive
     const float4 *fast_guards;    // per object: 2 x float4, box of the reference node that owns the leaf
     float scene_center[3];
     float scene_radius;           // bounds all primitive boxes (for the culling slack)

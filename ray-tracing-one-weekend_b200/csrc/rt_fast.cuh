@@ -298,7 +298,7 @@ __device__ __forceinline__ void fast_leaf(const DScene &S, FastTrav &T, const KE
         const float4 g0 = __ldg(S.fast_guards + 2 * (size_t)obj), g1 = __ldg(S.fast_guards + 2 * (size_t)obj + 1);
         if (guard_surely_passes(g0, g1, T, t) ||
             aabb_hit(g0.x, g0.y, g0.z, g1.x, g1.y, g1.z, T.r, T.tmin, T.tmax)) {   // the reference reaches this leaf
-            T.best = t; T.best_obj = obj; T.best_prim = pid;
+            T.best = t; T.best_obj = obj; T.best_prim = pid >= 0 ? pid : __float_as_int(g0.w);     // a sphere leaf: its one primitive
             T.bestc = fminf(t, T.tmax);
             T.eta = fminf(T.eta_g, fmaf(T.Kd, T.bestc, T.base));
         }
@@ -309,7 +309,7 @@ __device__ __forceinline__ void fast_leaf(const DScene &S, FastTrav &T, const KE
 __device__ __forceinline__ bool fast_result(const DScene &S, const FastTrav &T, float &t_out, int &prim_out) {
     if (T.best_obj < 0) return false;
     t_out = T.best;
-    prim_out = T.best_prim >= 0 ? T.best_prim : __ldg(&S.objects[T.best_obj]).w;   // sphere leaf: its single primitive
+    prim_out = T.best_prim;     // a sphere leaf's primitive id came with its guard box (fast_offer)
     return true;
 }
 

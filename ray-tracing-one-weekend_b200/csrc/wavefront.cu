@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
                     float t = 0.f; int pid = -1;
                     if (!fast_result(S, T, t, pid)) pid = -1;
                     *reinterpret_cast<float2 *>(W.idh + 2 * (size_t)slot + 1) = make_float2(t, __int_as_float(pid));
-                    cls = pid >= 0 ? __ldg(&S.materials[2 * __ldg(&S.prims[pid * 5]).y + 1]).w : 0;
+                    cls = pid >= 0 ? __ldg(&S.prim_class[pid]) : 0;
                     has_ray = false;
                 }
                 const unsigned same = __match_any_sync(full, cls);
@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_exact_kernel(DScene S, Wa
         float t = 0.f; int pid = -1; unsigned nv = 0, pt = 0;
         if (!closest_hit_exact<false>(S, r, 0.001f, FLT_MAX, &g, t, pid, nv, pt)) { t = 0.f; pid = -1; }
         *reinterpret_cast<float2 *>(W.idh + 2 * slot + 1) = make_float2(t, __int_as_float(pid));
-        cls = pid >= 0 ? __ldg(&S.materials[2 * __ldg(&S.prims[pid * 5]).y + 1]).w : 0;
+        cls = pid >= 0 ? __ldg(&S.prim_class[pid]) : 0;
     }
     const unsigned same = __match_any_sync(full, cls);
     if (cls >= 0) {
