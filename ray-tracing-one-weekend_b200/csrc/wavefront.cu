@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(256) wf_generate_kernel(WavefrontLaunch W, rto
 
 // ---- extend ------------------------------------------------------------------------------------------------
 template <int MINB>
-__global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, WavefrontLaunch W, int parity, int refill_below, int leaf_min) {
+__global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, WavefrontLaunch W, int parity, int refill_below, int leaf_min, int debug_exact_every) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     __shared__ uint2 s_stack[RTOW_WF_STACK_SMEM * 128];
@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
                         Ray r;
                         r.ox = a.x; r.oy = a.y; r.oz = a.z; r.time = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z;
                         root_ray(S, r);
-                        if (use_fast && fast_covers(S, r, 0.001f, FLT_MAX)) {
+                        if (use_fast && fast_covers(S, r, 0.001f, FLT_MAX) && !(debug_exact_every && mine % (unsigned)debug_exact_every == 0)) {
                             fast_begin(S, r, 0.001f, FLT_MAX, T);
                         } else {
                             // list scenes (nothing to cull) and rays outside the culling argument: the reference walk
@@ -416,6 +416,7 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
     static const int minb_env = [] { const char *e = getenv("RTOW_WF_MINB"); return e ? atoi(e) : 0; }();   // tuning knob
     const int minb = minb_env ? minb_env : (S.fast_nodes ? 5 : 8);
     static const int exact_env = [] { const char *e = getenv("RTOW_WF_EXACT_KERNEL"); return e ? atoi(e) : 1; }();   // 0: A/B against wf_extend_kernel
+    static const int debug_exact_every = [] { const char *e = getenv("RTOW_WF_DEBUG_EXACT_EVERY"); return e ? atoi(e) : 0; }();   // tests: every n-th slot takes the in-kernel fallback to the reference walk
     static const int exact_minb = [] { const char *e = getenv("RTOW_WF_EXACT_MINB"); return e ? atoi(e) : 8; }();
     const bool exact_walk = exact_env && !(W.L.traverse == RTOW_TRAVERSE_FAST && S.fast_nodes != nullptr);
     if (minb >= 8) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_extend_kernel<8>, 128, 0);
@@ -443,8 +444,8 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
         if (exact_walk && exact_minb >= 8) wf_extend_exact_kernel<8><<<(unsigned)(W.pool / 128), 128, 0, stream>>>(S, W, parity);
         else if (exact_walk && exact_minb >= 6) wf_extend_exact_kernel<6><<<(unsigned)(W.pool / 128), 128, 0, stream>>>(S, W, parity);
         else if (exact_walk) wf_extend_exact_kernel<5><<<(unsigned)(W.pool / 128), 128, 0, stream>>>(S, W, parity);
-        else if (minb >= 8) wf_extend_kernel<8><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min);
-        else wf_extend_kernel<5><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min);
+        else if (minb >= 8) wf_extend_kernel<8><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, debug_exact_every);
+        else wf_extend_kernel<5><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, debug_exact_every);
         if (sampled) cudaEventRecord(ev[1], stream);
         wf_shade_kernel<<<pool_blocks, 256, 0, stream>>>(S, W, cam, parity);
         if (sampled) cudaEventRecord(ev[2], stream);

@@ -92,6 +92,35 @@ def test_wavefront_equals_megakernel(gpu, abi, W, H, spp):
     assert sb.launches > 3
 
 
+def test_wavefront_fallback_to_the_reference_walk(gpu, abi, tmp_path):
+    """Rays the FAST culling argument does not cover take the reference walk inside wf_extend_kernel.  A debug knob sends
+    every 5th slot that way: the image must not change by a bit (FAST == EXACT hit for hit) and the ray counts must stay.
+    Run in a child process because the knob is read once."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import sys, numpy as np\n"
+        "sys.path.insert(0, %r)\n"
+        "import __graft_entry__ as e\n"
+        "pkg = e.load_package(); abi = pkg.abi\n"
+        "sys.path.insert(0, %r)\n"
+        "from conftest import earth_image\n"
+        "host = pkg.HostScene('random_ned', seed=12345, image=earth_image())\n"
+        "dev = pkg.DeviceScene(host.desc)\n"
+        "img, st = dev.render(pkg.main_camera(96, 54), abi.default_render_params(96, 54, 40, seed=4, kernel=abi.KERNEL_WAVEFRONT))\n"
+        "np.save(sys.argv[1], img); print(st.rays, st.paths)\n"
+    ) % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for knob in ("0", "5"):
+        path = str(tmp_path / f"img{knob}.npy")
+        r = subprocess.run([sys.executable, "-c", code, path], capture_output=True, text=True, env=dict(os.environ, RTOW_WF_DEBUG_EXACT_EVERY=knob))
+        assert r.returncode == 0, r.stdout + r.stderr
+        outs.append((np.load(path), r.stdout.split()[-2:]))
+    assert outs[0][1] == outs[1][1]                       # same ray and path counts
+    assert outs[0][0].tobytes() == outs[1][0].tobytes()   # same image, bit for bit
+
+
 def test_render_is_deterministic_and_shard_invariant(gpu, abi):
     """spp sharding: the union of the shards' samples is the full image's sample set."""
     import torch
