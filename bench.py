@@ -324,7 +324,7 @@ def run_product(args):
         hbm_note = dom["kernel"] + ": slot state read + hit/queue written per launch; the pool is partly L2-resident and the kernel is issue-bound, not HBM-bound"
         try:      # measured DRAM bytes per launch of the same kernel on the same scene and pool (one ncu --set full capture)
             t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["wf_extend_kernel"]
-            if (W, H, args.scene) == (WIDTH, HEIGHT, SCENE) and prof.pool_slots == 1 << 20:
+            if (W, H, args.scene) == (WIDTH, HEIGHT, SCENE) and prof.pool_slots == int(t.get("pool_slots", 1 << 20)):
                 traffic = int(t["dram_bytes_per_launch"])
         except Exception:
             traffic = None
