@@ -165,7 +165,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=JSON_OUT, flush=True)
 
 
 # ---- the product arm --------------------------------------------------------------------------
@@ -365,7 +365,7 @@ def run_product(args):
         "bvh_hit": bvh,
         "cpu_baseline": cpu,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=JSON_OUT, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -437,7 +437,16 @@ def bvh_hit_bench(pkg, abi, torch, dev_t, stream, args):
     return out
 
 
+JSON_OUT = sys.stdout
+
+
 def main():
+    # stdout carries the one JSON line and nothing else: whatever a library writes to file descriptor 1 (NCCL's version banner
+    # does, NCCL_DEBUG_FILE notwithstanding) is sent to stderr, and the line goes to a private duplicate of the real stdout
+    global JSON_OUT
+    sys.stdout.flush()
+    JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
