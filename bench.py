@@ -104,6 +104,14 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def describe_images(images, scene):
+    """What the image texture of the rendered scene is: both arms print it, so a mismatch cannot go unnoticed."""
+    if not len(images):
+        return "absent (glass-sphere fallback, scenes.h:202-207)" if scene.startswith("random") else "none in this scene"
+    fn = "1_earth_8k.jpg" if scene.endswith("_ned") else "earth1300x1300.jpg"
+    return ", ".join(f"{fn} {im.shape[1]}x{im.shape[0]}" for im in images)
+
+
 def host_threads():
     try:
         return len(os.sched_getaffinity(0))
@@ -118,6 +126,8 @@ def reference_render_sample(threads, budget_s):
     if ob.have_ref():
         ref = ob.RefOracle()
         sc = ref.scene(SCENE, seed=SCENE_SEED, wrap=True)
+        global REF_IMAGE_TEXTURE
+        REF_IMAGE_TEXTURE = describe_images(sc.arrays()["images"], SCENE)
         cam = ref.main_camera(WIDTH, HEIGHT)
         probe = sc.render(cam, 480, 270, 1, seed=RENDER_SEED, threads=threads)      # calibration, untimed
         rate = probe["paths"] / max(probe["seconds"], 1e-6)
@@ -159,7 +169,7 @@ def run_reference(args):
         "impl": "reference", "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": sample},
+        "config": {"workload": WORKLOAD, "sample": sample, "image_texture": REF_IMAGE_TEXTURE},
         "mrays_per_s": rays / secs / 1e6,
         "cpu_baseline": {"value": value, "unit": "Mpaths/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -192,7 +202,11 @@ def run_product(args):
     sptr = stream.cuda_stream
 
     W, H, spp = args.width, args.height, args.spp
-    host = pkg.HostScene(args.scene, seed=SCENE_SEED, wrap=True)
+    host = pkg.HostScene(args.scene, seed=SCENE_SEED, wrap=True)      # image textures decoded by the library (include/rtow/jpeg_decode.h)
+    image_texture = describe_images(host.arrays()["images"], args.scene)
+    if args.scene.startswith("random") and image_texture.startswith("absent"):
+        raise SystemExit("bench.py: input_images/1_earth_8k.jpg not found -- the scene would fall back to the glass sphere "
+                         "(scenes.h:202-207) and no longer be the reference's; run __graft_entry__.build() or set RTOW_INPUT_IMAGES")
     scene = pkg.DeviceScene(host.desc, device=local)
     cam = pkg.main_camera(W, H)
     # spp sharding: rank g renders samples [b_g, b_g + n_g); the union is [0, spp) for any world size
@@ -346,7 +360,7 @@ def run_product(args):
         "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD if (W, H, spp, args.scene) == (WIDTH, HEIGHT, SPP, SCENE) else f"{args.scene} scene {W}x{H}, {spp} spp, depth {DEPTH}",
-                   "scene_seed": SCENE_SEED, "render_seed": RENDER_SEED, "parallelism": f"spp-sharded x{world}, NCCL sum-reduce of fp32 accumulators",
+                   "image_texture": image_texture, "scene_seed": SCENE_SEED, "render_seed": RENDER_SEED, "parallelism": f"spp-sharded x{world}, NCCL sum-reduce of fp32 accumulators",
                    "kernel": kernel_name, "traverse": {1: "exact", 2: "fast"}[wc.traverse],
                    "l2": "flushed between timed iterations (256 MiB fill); scene is L2-resident by design"},
         "mrays_per_s": rays_per_step / (ms_step * 1e-3) / 1e6,
@@ -359,7 +373,8 @@ def run_product(args):
                           "traffic": traffic, "peak_source": f"{sms} SMs x 128 fp32 lanes x {mhz:.0f} MHz (clocks.max.sm)",
                           "whole_step_achieved": step_tops, "whole_step_frac": step_tops / peak_tops,
                           "ops_per_ray_incl_shading": ops_per_ray, "node_visits_per_ray": wc.node_visits_per_ray,
-                          "prim_tests_per_ray": wc.prim_tests_per_ray, "noise_evals_per_ray": wc.noise_evals_per_ray}, **dom),
+                          "prim_tests_per_ray": wc.prim_tests_per_ray, "noise_evals_per_ray": wc.noise_evals_per_ray,
+                          "image_evals_per_ray": wc.image_evals_per_ray, "checker_evals_per_ray": wc.checker_evals_per_ray}, **dom),
         "roofline_hbm": {"bound": "hbm", "achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak, "traffic": traffic,
                          "algorithmic_bytes_per_launch": alg_bytes, "peak_source": hbm_src, "note": hbm_note},
         "bvh_hit": bvh,
@@ -438,6 +453,7 @@ def bvh_hit_bench(pkg, abi, torch, dev_t, stream, args):
 
 
 JSON_OUT = sys.stdout
+REF_IMAGE_TEXTURE = "decoded by the library (C port arm)"
 
 
 def main():

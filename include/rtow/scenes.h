@@ -11,16 +11,23 @@
 // Unused locals of the reference that allocate but never reach the scene are not reproduced
 // unless they draw random numbers (none do).
 //
-// Image textures: the reference decodes JPEGs with its vendored stb_image (out of scope here,
-// SURVEY section 2 row 22).  load_image() reads binary PPM (P6); for "foo.jpg" it looks for
-// "foo.ppm" beside it.  When nothing can be loaded the builders substitute the glass sphere,
-// as the reference does when stbi_load returns NULL (scenes.h:104-109,202-207).
+// Image textures: the reference decodes ./input_images/*.jpg with its vendored stb_image
+// (scenes.h:47,140).  load_image() decodes the same files with rtow/jpeg_decode.h, which reproduces
+// stb_image's integer arithmetic byte for byte (tests/test_jpeg_decode.py), so the flattened scene
+// equals the reference's without any override.  The reference's paths are relative to the CWD; when
+// the file is not there, load_image() also looks in image_dir() (rtow_host_set_image_dir, or the
+// environment variable RTOW_INPUT_IMAGES: a directory that holds the .jpg files themselves).
+// Binary PPM (P6) is read as well.  When nothing can be loaded the builders substitute the glass
+// sphere, as the reference does when stbi_load returns NULL (scenes.h:104-109,202-207).
 #pragma once
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
+#include <vector>
 
+#include "jpeg_decode.h"
 #include "scene_api.h"
 
 namespace rtow {
@@ -57,16 +64,35 @@ inline unsigned char *load_ppm(const char *path, int *nx, int *ny) {
 struct ImageOverride { unsigned char *data = nullptr; int nx = 0, ny = 0; };
 inline ImageOverride &image_override() { static ImageOverride o; return o; }
 
+// Where else to look for "./input_images/<file>" (empty: the CWD-relative path only, like the reference).
+inline std::string &image_dir() {
+    static std::string d = [] { const char *e = std::getenv("RTOW_INPUT_IMAGES"); return std::string(e ? e : ""); }();
+    return d;
+}
+
+inline unsigned char *load_image_file(const std::string &path, int *nx, int *ny, int *nn) {
+    if (unsigned char *p = load_ppm(path.c_str(), nx, ny)) { *nn = 3; return p; }
+    return jpeg::load_file(path.c_str(), nx, ny, nn);
+}
+
 inline unsigned char *load_image(const char *path, int *nx, int *ny, int *nn) {
     *nn = 3;
     ImageOverride &o = image_override();
     if (o.data) { *nx = o.nx; *ny = o.ny; return o.data; }
-    if (unsigned char *p = load_ppm(path, nx, ny)) return p;
     std::string s(path);
-    size_t dot = s.rfind('.');
-    if (dot != std::string::npos) {
-        s = s.substr(0, dot) + ".ppm";
-        if (unsigned char *p = load_ppm(s.c_str(), nx, ny)) return p;
+    std::vector<std::string> tries{s};
+    const size_t slash = s.find_last_of('/');
+    const std::string base = slash == std::string::npos ? s : s.substr(slash + 1);
+    if (!image_dir().empty()) tries.push_back(image_dir() + "/" + base);
+    for (const std::string &t : tries) {
+        int c = 0;
+        if (unsigned char *p = load_image_file(t, nx, ny, &c)) {
+            if (c == 3) { *nn = 3; return p; }
+            delete[] p;          // ImageTexture indexes RGB triples (texture.h:72-76): a grey file cannot stand in
+        }
+        const size_t dot = t.rfind('.');
+        if (dot != std::string::npos)
+            if (unsigned char *p = load_ppm((t.substr(0, dot) + ".ppm").c_str(), nx, ny)) return p;
     }
     return nullptr;
 }

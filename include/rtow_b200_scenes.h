@@ -28,6 +28,17 @@ void rtow_host_scene_free(rtow_host_scene *scene);
  * ./input_images/<name> (scenes.h:47,140); nx = 0 clears the override. */
 int rtow_host_set_image(const uint8_t *rgb, int32_t nx, int32_t ny);
 
+/* Directory searched for the builders' image files ("1_earth_8k.jpg", "earth1300x1300.jpg") when the
+ * reference's CWD-relative path ./input_images/<name> (scenes.h:47,140) does not exist; NULL or ""
+ * clears it (default: the environment variable RTOW_INPUT_IMAGES). */
+int rtow_host_set_image_dir(const char *dir);
+
+/* Decodes a JPEG (baseline or progressive Huffman, 8 bit, 1 or 3 components) or binary PPM file the way
+ * the reference's stbi_load(path,&nx,&ny,&nn,0) does (scenes.h:47,140; byte-identical texels).  On success
+ * *rgb_out is a buffer of nx*ny*channels bytes to be released with rtow_host_free_image. */
+int rtow_host_decode_image(const char *path, uint8_t **rgb_out, int32_t *nx, int32_t *ny, int32_t *channels);
+void rtow_host_free_image(uint8_t *rgb);
+
 /* Camera(lookFrom, lookAt, up, vFoV, aspect, aperture, focusDistance, t0, t1) of camera.h:13
  * -> the POD frame of camera.h:315-342. */
 int rtow_host_camera(const float look_from[3], const float look_at[3], const float up[3], float vfov,

@@ -17,6 +17,8 @@ from .binding import (  # noqa: F401
     lib,
     lib_path,
     HostScene,
+    decode_image,
+    image_dir,
     DeviceScene,
     make_camera,
     main_camera,
@@ -26,5 +28,5 @@ from .binding import (  # noqa: F401
     oriented_camera,
 )
 
-__all__ = ["abi", "RtowError", "lib", "lib_path", "HostScene", "DeviceScene", "make_camera", "main_camera",
+__all__ = ["abi", "RtowError", "lib", "lib_path", "HostScene", "decode_image", "image_dir", "DeviceScene", "make_camera", "main_camera",
            "write_ppm", "write_pfm", "write_exr", "oriented_camera", "ProgressiveRender"]

@@ -60,6 +60,9 @@ def lib():
         "rtow_host_scene_desc": (P(abi.SceneDesc), [vp]),
         "rtow_host_scene_free": (None, [vp]),
         "rtow_host_set_image": (C.c_int, [vp, i32, i32]),
+        "rtow_host_set_image_dir": (C.c_int, [C.c_char_p]),
+        "rtow_host_decode_image": (C.c_int, [C.c_char_p, P(P(C.c_uint8)), P(i32), P(i32), P(i32)]),
+        "rtow_host_free_image": (None, [P(C.c_uint8)]),
         "rtow_host_camera": (C.c_int, [P(f32 * 3), P(f32 * 3), P(f32 * 3), f32, f32, f32, f32, f32, f32, P(abi.Camera)]),
         "rtow_write_ppm": (C.c_int, [C.c_char_p, vp, i32, i32]),
         "rtow_write_pfm": (C.c_int, [C.c_char_p, vp, i32, i32]),
@@ -77,7 +80,7 @@ EXPORTED_SYMBOLS = [
     "rtow_device_count", "rtow_scene_create", "rtow_scene_destroy", "rtow_trace_rays", "rtow_trace_rays_device",
     "rtow_render", "rtow_render_accumulate_device", "rtow_render_accumulate_moments_device", "rtow_stream_stats", "rtow_resolve_device", "rtow_trace_counters", "rtow_render_counters", "rtow_render_profile",
     "rtow_last_error", "rtow_build_info", "rtow_host_scene_build", "rtow_host_scene_desc", "rtow_host_scene_free",
-    "rtow_host_set_image", "rtow_host_camera", "rtow_write_ppm", "rtow_write_pfm", "rtow_write_exr", "rtow_host_camera_oriented",
+    "rtow_host_set_image", "rtow_host_set_image_dir", "rtow_host_decode_image", "rtow_host_free_image", "rtow_host_camera", "rtow_write_ppm", "rtow_write_pfm", "rtow_write_exr", "rtow_host_camera_oriented",
 ]
 
 
@@ -112,11 +115,41 @@ def main_camera(width, height):
     return make_camera((0, 0, 0), (1, 0, 0), (0, 0, -1), 60.0, float(width) / float(height), 2.0, 1000.0, 0.0, 1.0)
 
 
+def image_dir():
+    """Where the builders' ./input_images/*.jpg (scenes.h:47,140) are looked for when the CWD does not have them:
+    $RTOW_INPUT_IMAGES, else the copies build() stages next to the library (git-ignored, they travel with the snapshot),
+    else the reference checkout."""
+    for d in (os.environ.get("RTOW_INPUT_IMAGES"), os.path.join(_HERE, "input_images"),
+              "/root/reference/rayTracingOneWeekend/input_images"):
+        if d and os.path.isfile(os.path.join(d, "1_earth_8k.jpg")):
+            return d
+    return None
+
+
+def decode_image(path):
+    """The library's own JPEG / PPM decoder (include/rtow/jpeg_decode.h): texels as stbi_load returns them."""
+    L = lib()
+    px, nx, ny, nc = C.POINTER(C.c_uint8)(), C.c_int32(), C.c_int32(), C.c_int32()
+    _check(L.rtow_host_decode_image(str(path).encode(), C.byref(px), C.byref(nx), C.byref(ny), C.byref(nc)))
+    try:
+        return np.ctypeslib.as_array(px, shape=(ny.value, nx.value, nc.value)).copy()
+    finally:
+        L.rtow_host_free_image(px)
+
+
 class HostScene:
-    """A scene built by the host-side scene API (mirrors scenes.h) and flattened."""
+    """A scene built by the host-side scene API (mirrors scenes.h) and flattened.
+
+    image=None: the builders load ./input_images/*.jpg themselves like the reference (decoded by the library);
+    image=array: those loads return the given texels; image=False: loads fail, i.e. the reference's glass-sphere
+    fallback (scenes.h:104-109,202-207)."""
 
     def __init__(self, name, seed=12345, n=0, wrap=True, image=None):
         L = lib()
+        d = image_dir() if image is None else None
+        _check(L.rtow_host_set_image_dir(d.encode() if d else (b"/nonexistent" if image is False else None)))
+        if image is False:
+            image = None
         if image is not None:
             img = np.ascontiguousarray(image, dtype=np.uint8)
             assert img.ndim == 3 and img.shape[2] == 3

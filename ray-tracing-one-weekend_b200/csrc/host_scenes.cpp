@@ -36,6 +36,23 @@ int rtow_host_set_image(const uint8_t *rgb, int32_t nx, int32_t ny) {
     return RTOW_OK;
 }
 
+int rtow_host_set_image_dir(const char *dir) {
+    rtow::api::image_dir() = dir ? dir : "";
+    return RTOW_OK;
+}
+
+int rtow_host_decode_image(const char *path, uint8_t **rgb_out, int32_t *nx, int32_t *ny, int32_t *channels) {
+    if (!path || !rgb_out || !nx || !ny || !channels) return rtow::set_error(RTOW_ERR_INVALID_ARG, "rtow_host_decode_image: null argument");
+    *rgb_out = nullptr;
+    int w = 0, h = 0, c = 0;
+    unsigned char *p = rtow::api::load_image_file(path, &w, &h, &c);
+    if (!p) return rtow::set_error(RTOW_ERR_IO, std::string("cannot decode ") + path);
+    *rgb_out = p; *nx = w; *ny = h; *channels = c;
+    return RTOW_OK;
+}
+
+void rtow_host_free_image(uint8_t *rgb) { delete[] rgb; }
+
 int rtow_host_scene_build(const char *name, uint64_t seed, int n, int wrap, rtow_host_scene **out) {
     using namespace rtow::api;
     if (!name || !out) return rtow::set_error(RTOW_ERR_INVALID_ARG, "rtow_host_scene_build: null argument");

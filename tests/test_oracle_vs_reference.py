@@ -30,9 +30,22 @@ def test_host_scene_api_flattens_like_the_reference(pkg, ob, ref, name, kw):
     through the same flatten.h: every array byte-identical (primitive order, BVH topology and boxes from the
     reference's qsort build, wrapper chains, materials, textures, Perlin tables, decoded JPEG texels)."""
     rs = ref.scene(name, seed=12345, n=kw.get("n", 0), wrap=kw.get("wrap", True))
-    img = _earth(ob, ref, name) if name.startswith("random") else None
-    hs = pkg.HostScene(name, seed=12345, n=kw.get("n", 0), wrap=kw.get("wrap", True), image=img)
-    _same_arrays(hs.arrays(), rs.arrays(), name)
+    # no image override: the library decodes input_images/*.jpg itself (include/rtow/jpeg_decode.h), the reference with
+    # its stb_image (scenes.h:47,140), and the texel arrays must come out byte-identical
+    hs = pkg.HostScene(name, seed=12345, n=kw.get("n", 0), wrap=kw.get("wrap", True))
+    a, b = hs.arrays(), rs.arrays()
+    if name.startswith("random"):
+        assert len(a["images"]) == 1 and len(b["images"]) == 1, "the image texture must be present on both sides (no glass-sphere fallback)"
+    _same_arrays(a, b, name)
+
+
+def test_failed_image_load_gives_the_glass_sphere_like_the_reference(pkg, abi):
+    """scenes.h:104-109,202-207: stbi_load returning NULL silently substitutes a Dielectric sphere."""
+    h1, h2 = pkg.HostScene("random_ned", seed=12345, wrap=True), pkg.HostScene("random_ned", seed=12345, wrap=True, image=False)
+    with_img, without = h1.arrays(), h2.arrays()          # views into the scenes' own storage: keep h1, h2 alive
+    assert len(with_img["images"]) == 1 and len(without["images"]) == 0
+    assert (with_img["textures"]["type"] == abi.TEX_IMAGE).sum() == 1 and (without["textures"]["type"] == abi.TEX_IMAGE).sum() == 0
+    assert (without["materials"]["type"] == abi.MAT_DIELECTRIC).sum() == (with_img["materials"]["type"] == abi.MAT_DIELECTRIC).sum() + 1
 
 
 @pytest.mark.parametrize("name,kw", SCENES + [("bvh_stress", dict(n=20000))], ids=[s[0] for s in SCENES] + ["bvh_stress"])
