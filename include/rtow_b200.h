@@ -263,6 +263,22 @@ int rtow_render(rtow_scene *scene, const rtow_camera *cam, const rtow_render_par
 int rtow_render_accumulate_device(rtow_scene *scene, const rtow_camera *cam,
                                   const rtow_render_params *params, float *d_accum, void *stream);
 
+/* rtow_render_accumulate_device for callers that cannot allocate device memory at call time (code under CUDA graph
+ * capture of the surrounding work, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE
+ * REFERENCE.  Same result as rtow_render_accumulate_device (wavefront
+ * kernels), but the path pool, class queues and fixed-point pixel sums live in one file-scope static __device__ array
+ * of RTOW_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit; the call itself performs no
+ * cudaMalloc / cudaFree / pinned allocation.  Limits: at most RTOW_NOALLOC_MAX_PIXELS pixels per call (use
+ * row_begin / row_count bands for larger frames), else RTOW_ERR_INVALID_ARG with a message; the pool is capped at
+ * RTOW_NOALLOC_MAX_POOL paths in flight (throughput below the allocating entry's on large frames).  All calls on a
+ * device share the array: calls that overlap on the GPU (two streams, two host threads) race -- serialise them.
+ * Synchronises `stream` before returning, like the allocating entry.  params->kernel = RTOW_KERNEL_MEGA is refused. */
+#define RTOW_NOALLOC_MAX_POOL 65536
+#define RTOW_NOALLOC_MAX_PIXELS 262144
+#define RTOW_NOALLOC_SCRATCH_BYTES (RTOW_NOALLOC_MAX_POOL * 32 * 2 + RTOW_NOALLOC_MAX_POOL * 16 * 4 + RTOW_NOALLOC_MAX_PIXELS * 3 * 8 + 512)
+int rtow_render_accumulate_device_noalloc(rtow_scene *scene, const rtow_camera *cam,
+                                          const rtow_render_params *params, float *d_accum, void *stream);
+
 /* The same, plus the sum of SQUARED per-sample radiance into d_accum_sq (W*H*3 floats, added to; null = not wanted):
  * with the sample count this is the per-pixel variance image, kept across calls for progressive rendering and
  * checkpoint / resume (the reference re-renders from scratch, main.cpp:247).  Wavefront kernels

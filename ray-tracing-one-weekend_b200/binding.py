@@ -48,6 +48,7 @@ def lib():
         "rtow_trace_rays_device": (C.c_int, [vp, vp, u64, vp, C.c_int, u64, vp]),
         "rtow_render": (C.c_int, [vp, P(abi.Camera), P(abi.RenderParams), vp, vp, P(abi.Stats)]),
         "rtow_render_accumulate_device": (C.c_int, [vp, P(abi.Camera), P(abi.RenderParams), vp, vp]),
+        "rtow_render_accumulate_device_noalloc": (C.c_int, [vp, P(abi.Camera), P(abi.RenderParams), vp, vp]),
         "rtow_render_accumulate_moments_device": (C.c_int, [vp, P(abi.Camera), P(abi.RenderParams), vp, vp, vp]),
         "rtow_stream_stats": (C.c_int, [vp, vp, P(abi.Stats)]),
         "rtow_resolve_device": (C.c_int, [vp, vp, i32, i32, i32, vp, vp, vp]),
@@ -78,7 +79,7 @@ def lib():
 
 EXPORTED_SYMBOLS = [
     "rtow_device_count", "rtow_scene_create", "rtow_scene_destroy", "rtow_trace_rays", "rtow_trace_rays_device",
-    "rtow_render", "rtow_render_accumulate_device", "rtow_render_accumulate_moments_device", "rtow_stream_stats", "rtow_resolve_device", "rtow_trace_counters", "rtow_render_counters", "rtow_render_profile",
+    "rtow_render", "rtow_render_accumulate_device", "rtow_render_accumulate_device_noalloc", "rtow_render_accumulate_moments_device", "rtow_stream_stats", "rtow_resolve_device", "rtow_trace_counters", "rtow_render_counters", "rtow_render_profile",
     "rtow_last_error", "rtow_build_info", "rtow_host_scene_build", "rtow_host_scene_desc", "rtow_host_scene_free",
     "rtow_host_set_image", "rtow_host_set_image_dir", "rtow_host_decode_image", "rtow_host_free_image", "rtow_host_camera", "rtow_write_ppm", "rtow_write_pfm", "rtow_write_exr", "rtow_host_camera_oriented",
 ]
@@ -249,6 +250,10 @@ class DeviceScene:
 
     def accumulate_device(self, cam, params, d_accum_ptr, stream=None):
         _check(lib().rtow_render_accumulate_device(self._h, C.byref(cam), C.byref(params), d_accum_ptr, stream))
+
+    def accumulate_device_noalloc(self, cam, params, d_accum_ptr, stream=None):
+        """Static-scratch variant: no device allocation at call time (include/rtow_b200.h)."""
+        _check(lib().rtow_render_accumulate_device_noalloc(self._h, C.byref(cam), C.byref(params), d_accum_ptr, stream))
 
     def accumulate_moments_device(self, cam, params, d_accum_ptr, d_accum_sq_ptr, stream=None):
         _check(lib().rtow_render_accumulate_moments_device(self._h, C.byref(cam), C.byref(params), d_accum_ptr, d_accum_sq_ptr, stream))

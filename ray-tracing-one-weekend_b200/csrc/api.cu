@@ -257,9 +257,74 @@ int check_render_args(const rtow_scene *s, const rtow_camera *cam, const rtow_re
     return RTOW_OK;
 }
 
+// ---- scratch of rtow_render_accumulate_device_noalloc -------------------------------------------------------------
+// The wavefront path's work memory (path pool, class queues, fixed-point pixel sums, control words) in ONE file-scope
+// device array, so that the entry point below allocates nothing.  Every GPU that loads the library holds these
+// RTOW_NOALLOC_SCRATCH_BYTES (~14 MB) until the process exits.  In host code `g_noalloc_scratch` is only a stand-in for the
+// symbol, not a device address: the address comes from cudaGetSymbolAddress, once per device, with that device current.
+constexpr size_t NA_POOL = RTOW_NOALLOC_MAX_POOL, NA_PIXELS = RTOW_NOALLOC_MAX_PIXELS;
+constexpr size_t NA_OFF_RAY = 0;
+constexpr size_t NA_OFF_IDH = NA_OFF_RAY + NA_POOL * 32;
+constexpr size_t NA_OFF_QUEUE = NA_OFF_IDH + NA_POOL * 32;
+constexpr size_t NA_OFF_FIXED = NA_OFF_QUEUE + NA_POOL * RTOW_WF_MAX_CLASSES * 4;
+constexpr size_t NA_OFF_COUNTS = NA_OFF_FIXED + NA_PIXELS * 3 * 8;
+constexpr size_t NA_OFF_CONTROL = NA_OFF_COUNTS + 256;
+constexpr size_t NA_BYTES = NA_OFF_CONTROL + 256;
+static_assert(2 * RTOW_WF_MAX_CLASSES * 4 <= 256 && RTOW_WF_CONTROL_WORDS * 8 <= 256, "control blocks fit their 256-byte cells");
+static_assert(NA_BYTES == RTOW_NOALLOC_SCRATCH_BYTES, "header and layout agree on the size of the static scratch");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_BYTES];
+
+constexpr int NA_MAX_DEVICES = 64;
+unsigned char *g_noalloc_ptr[NA_MAX_DEVICES];     // device address of the array on each device (null: not asked yet)
+std::mutex g_noalloc_mu;
+
+// the device must be current
+int noalloc_scratch(int device, unsigned char **out) {
+    if (device < 0 || device >= NA_MAX_DEVICES) return set_error(RTOW_ERR_INVALID_ARG, "noalloc: device index beyond the table");
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void *p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) return set_error(RTOW_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+        g_noalloc_ptr[device] = (unsigned char *)p;
+    }
+    *out = g_noalloc_ptr[device];
+    return RTOW_OK;
+}
+
 }  // namespace
 
 extern "C" {
+
+int rtow_render_accumulate_device_noalloc(rtow_scene *s, const rtow_camera *cam, const rtow_render_params *params, float *d_accum, void *stream) {
+    RenderLaunch L;
+    if (int rc = check_render_args(s, cam, params, &L)) return rc;
+    if (!d_accum) return set_error(RTOW_ERR_INVALID_ARG, "rtow_render_accumulate_device_noalloc: null accumulator");
+    if (params->kernel == RTOW_KERNEL_MEGA) return set_error(RTOW_ERR_UNSUPPORTED, "rtow_render_accumulate_device_noalloc runs the wavefront kernels only");
+    if ((size_t)L.pixel_count > NA_PIXELS)
+        return set_error(RTOW_ERR_INVALID_ARG, "rtow_render_accumulate_device_noalloc: " + std::to_string(L.pixel_count) + " pixels in this call, the static scratch holds at most " +
+                                                   std::to_string(NA_PIXELS) + " (RTOW_NOALLOC_MAX_PIXELS); render bands of rows or use rtow_render_accumulate_device");
+    CUDA_TRY(cudaSetDevice(s->device));
+    unsigned char *base = nullptr;
+    if (int rc = noalloc_scratch(s->device, &base)) return rc;
+    const unsigned long long items = (unsigned long long)(((long long)L.pixel_count + 31) / 32) * 32ull * (unsigned)L.sample_count;
+    long long pool = (long long)std::min<unsigned long long>(items, (unsigned long long)NA_POOL);
+    pool = (pool + 255) / 256 * 256;           // NA_POOL is a multiple of 256
+    WavefrontLaunch W;
+    std::memset(&W, 0, sizeof W);
+    W.L = L; W.pool = (int)pool; W.total_items = items;
+    W.ray = (float4 *)(base + NA_OFF_RAY); W.idh = (int4 *)(base + NA_OFF_IDH);
+    W.queue = (int *)(base + NA_OFF_QUEUE); W.counts = (unsigned *)(base + NA_OFF_COUNTS);
+    W.fixed = (unsigned long long *)(base + NA_OFF_FIXED); W.fixed_sq = nullptr;
+    W.control = (unsigned long long *)(base + NA_OFF_CONTROL);
+    W.next_item = W.control; W.dead_slots = W.control + 1; W.extend_head = W.control + 2; W.stats = W.control + 3;
+    // The array keeps the previous call's contents: run_wavefront clears what must start at zero (pixel sums, control words,
+    // queue lengths) and wf_generate_kernel rewrites every slot of the pool it uses; stale slots and queue entries beyond
+    // are never read.  Its progress polls land in a local (pageable) word: no pinned allocation either.
+    unsigned long long polled[2] = {0ull, 0ull};
+    CUDA_TRY(run_wavefront(s->d, *cam, W, d_accum, nullptr, polled, (cudaStream_t)stream, nullptr, nullptr));
+    return RTOW_OK;
+}
 
 int rtow_device_count(void) {
     int n = 0;
