@@ -36,6 +36,7 @@ def load_package():
 abi = load_package().abi
 
 REF_SO = os.path.join(_HERE, "_ref", "libref_oracle.so")
+REF_DOF_SO = os.path.join(_HERE, "_ref", "libref_oracle_dof.so")      # the reference built with CAMERA_DOF_EN 1
 PORT_SO = os.path.join(_HERE, "_build", "librtow_oracle.so")
 REF_IMAGE_DIR = os.path.join(_HERE, "_ref")
 
@@ -51,6 +52,10 @@ def build(verbose=False):
 
 def have_ref():
     return os.path.exists(REF_SO)
+
+
+def have_ref_dof():
+    return os.path.exists(REF_DOF_SO)
 
 
 def _ptr(a):
@@ -115,10 +120,11 @@ class RefScene:
 class RefOracle:
     """The reference's own CPU implementation (world->hit, color, getRay, textures...)."""
 
-    def __init__(self):
-        if not have_ref():
-            raise RuntimeError(f"{REF_SO} missing: run `make -C oracle` where /root/reference exists")
-        L = C.CDLL(REF_SO)
+    def __init__(self, dof=False):
+        so = REF_DOF_SO if dof else REF_SO
+        if not os.path.exists(so):
+            raise RuntimeError(f"{so} missing: run `make -C oracle` where /root/reference exists")
+        L = C.CDLL(so)
         vp, u64 = C.c_void_p, C.c_uint64
         L.ref_last_error.restype = C.c_char_p
         L.ref_set_image_dir.argtypes = [C.c_char_p]

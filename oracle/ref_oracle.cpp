@@ -26,6 +26,14 @@
 
 #include <cfloat>
 #include <random>
+#ifdef REF_ORACLE_DOF
+// Second build of this same file (oracle/Makefile: _ref/libref_oracle_dof.so) with the reference's depth-of-field branch
+// compiled in (camera.h:125-126, mathUtilities.h:11-17).  defines.h is #pragma once: including it first and re-defining
+// the switch leaves the file untouched and makes every later #include "defines.h" a no-op.
+#include "defines.h"
+#undef CAMERA_DOF_EN
+#define CAMERA_DOF_EN 1
+#endif
 #define mt19937_64 mt19937_64 thread_local
 #include "rngs.h"
 #undef mt19937_64

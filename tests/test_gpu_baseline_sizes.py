@@ -1,0 +1,66 @@
+"""-m gpu: parity at the sizes BASELINE.json quotes, through the C ABI.
+
+  * configs[4]: 1 M random spheres under the reference's BvhNode build, 2^20 coherent + 2^20 incoherent rays, both
+    traversals against the REFERENCE's own world->hit() (oracle/_ref; bvhNode.h:66-96, sphere.h:20-69): primitive id and
+    material id exact, t / point / normal bit-identical (north_star asks for 1e-5 relative).
+  * configs[1] and configs[3] frame sizes: one 1920x1080 and one 3840x2160 frame at 1 spp against the port oracle (same
+    Philox streams): ray counts equal, pixel sums within 2e-4.  This is where the 64-bit work-item arithmetic, pool
+    regeneration over many bounce iterations and the padded pixel groups get exercised at scale.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import bits
+
+pytestmark = pytest.mark.gpu
+
+
+def test_one_million_spheres_match_the_reference_on_2_20_rays_per_class(gpu, abi, ob, port):
+    n_spheres, seed = 1000000, 12345
+    host = gpu.HostScene("bvh_stress", seed=seed, n=n_spheres)
+    dev = gpu.DeviceScene(host.desc)
+    sets = {"coherent": gpu.raysets.coherent_rays(1024), "incoherent": gpu.raysets.incoherent_rays(1 << 20, seed=7, extent=100.0)}
+    if ob.have_ref():
+        ref = ob.RefOracle()
+        rs = ref.scene("bvh_stress", seed=seed, n=n_spheres)
+        threads = len(os.sched_getaffinity(0))
+        oracle = lambda rays: rs.trace(rays, threads=threads)[0]
+        stride = 1
+    else:                       # no reference build on this box: the port oracle (pinned to the reference elsewhere) on a subsample
+        oracle = lambda rays: port.trace(host.desc, rays)
+        stride = 16
+    for name, rays in sets.items():
+        assert len(rays) == 1 << 20
+        rays = np.ascontiguousarray(rays[::stride])
+        want = oracle(rays)
+        assert 0.05 < (want["prim_id"] >= 0).mean() < 1.0, name
+        hit = want["prim_id"] >= 0
+        for mode, tag in ((abi.TRAVERSE_FAST, "fast"), (abi.TRAVERSE_EXACT, "exact")):
+            got, _ = dev.trace(rays, traverse=mode)
+            bad = np.flatnonzero(got["prim_id"] != want["prim_id"])
+            assert len(bad) == 0, f"{name}/{tag}: {len(bad)} primitive ids differ, first at rays {bad[:8]}"
+            assert np.array_equal(got["mat_id"], want["mat_id"]), f"{name}/{tag}: material ids"
+            for k in ("t", "p", "n"):
+                assert np.array_equal(bits(got[k][hit]), bits(want[k][hit])), f"{name}/{tag}: {k} not bit-identical"
+            rel = np.abs(got["t"][hit].astype(np.float64) - want["t"][hit]) / np.abs(want["t"][hit])
+            assert rel.max() <= 1e-5            # the north star's own gate, implied by the line above
+
+
+@pytest.mark.parametrize("name,W,H", [("random_ned", 1920, 1080), ("cornell_smoke_ned", 3840, 2160), ("cornell_ned", 1920, 1080)])
+def test_full_frame_at_one_sample_matches_the_oracle(gpu, abi, port, name, W, H):
+    host = gpu.HostScene(name, seed=12345, wrap=True)          # random_ned: with the reference's decoded 2048x1024 earth texture
+    if name.startswith("random"):
+        assert len(host.arrays()["images"]) == 1
+    dev = gpu.DeviceScene(host.desc)
+    cam = gpu.main_camera(W, H)
+    p = abi.default_render_params(W, H, 1, seed=2024)
+    img, st = dev.render(cam, p)
+    want = port.render(host.desc, cam, p)
+    assert st.paths == W * H
+    assert st.rays == want["rays"], "ray count differs: the GPU traced different paths than the oracle"
+    ref = want["sum"]
+    scale = max(1.0, float(np.percentile(np.abs(ref), 99.9)))
+    close = np.abs(img - ref) <= 2e-4 * np.maximum(scale, np.abs(ref))
+    assert close.mean() >= 0.9999, f"{name}: {100 * (1 - close.mean()):.4f}% of pixel channels off"
