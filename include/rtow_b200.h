@@ -25,6 +25,10 @@
  *                                  sample_begin+sample_count) only, sums left on
  *                                  the device (spp sharding across GPUs)
  * rtow_resolve_device              main.cpp:955-989 (mean, sqrt, 255.99, BGRA8)
+ * rtow_multi_create/render/destroy the worker-thread pool main() starts, one per core
+ *                                  (main.cpp:182-195), and its column interleave
+ *                                  (main.cpp:936): here one host thread per GPU, samples
+ *                                  per pixel split across the GPUs of the box
  * rtow_last_error                  std::cout/cerr prints (bvhNode.h:54,103)
  *
  * There is NO CPU fallback behind these symbols: without a CUDA device every
@@ -278,6 +282,24 @@ int rtow_render_accumulate_device(rtow_scene *scene, const rtow_camera *cam,
 #define RTOW_NOALLOC_SCRATCH_BYTES (RTOW_NOALLOC_MAX_POOL * 32 * 2 + RTOW_NOALLOC_MAX_POOL * 16 * 4 + RTOW_NOALLOC_MAX_PIXELS * 3 * 8 + 512)
 int rtow_render_accumulate_device_noalloc(rtow_scene *scene, const rtow_camera *cam,
                                           const rtow_render_params *params, float *d_accum, void *stream);
+
+/* ---- one frame on several GPUs of one box, from one process ------------------------------------------------------
+ * Replaces the reference's in-program parallelism (main.cpp:182-195 starts a worker per core, main.cpp:936 deals image
+ * columns to them): rtow_multi_create uploads the scene to every listed device (devices = NULL / n_devices <= 0: all
+ * visible ones; a device may be listed twice, its shards then share it); rtow_multi_render has one host thread per shard
+ * render a contiguous block of the sample indices of every pixel (same sample set, hence the same image up to fp32
+ * summation order, for any device count), then ONE kernel on devices[0] reads the shards' sum buffers in place over
+ * NVLink peer mappings (staged by cudaMemcpyPeer only where no mapping exists), adds them in shard order and applies
+ * main.cpp:955-989.  Outputs and params are rtow_render's (host buffers; bands of rows allowed).  stats: paths, rays
+ * and launches summed over the shards, kernel_ms of the slowest shard, total_ms of the whole call on devices[0].
+ * Synchronous; one call at a time per handle. */
+typedef struct rtow_multi rtow_multi;
+int rtow_multi_create(const rtow_scene_desc *desc, const int32_t *devices, int32_t n_devices, rtow_multi **out);
+int rtow_multi_render(rtow_multi *multi, const rtow_camera *cam, const rtow_render_params *params,
+                      float *rgb_linear_out, uint8_t *bgra8_out, rtow_stats *stats);
+int rtow_multi_device_count(const rtow_multi *multi);    /* shards */
+int rtow_multi_peer_mapped(const rtow_multi *multi);     /* shards on other devices that devices[0] reads in place */
+void rtow_multi_destroy(rtow_multi *multi);
 
 /* The same, plus the sum of SQUARED per-sample radiance into d_accum_sq (W*H*3 floats, added to; null = not wanted):
  * with the sample count this is the per-pixel variance image, kept across calls for progressive rendering and

@@ -20,6 +20,7 @@ from .binding import (  # noqa: F401
     decode_image,
     image_dir,
     DeviceScene,
+    MultiDeviceScene,
     make_camera,
     main_camera,
     write_ppm,
@@ -28,5 +29,5 @@ from .binding import (  # noqa: F401
     oriented_camera,
 )
 
-__all__ = ["abi", "RtowError", "lib", "lib_path", "HostScene", "decode_image", "image_dir", "DeviceScene", "make_camera", "main_camera",
+__all__ = ["abi", "RtowError", "lib", "lib_path", "HostScene", "decode_image", "image_dir", "DeviceScene", "MultiDeviceScene", "make_camera", "main_camera",
            "write_ppm", "write_pfm", "write_exr", "oriented_camera", "ProgressiveRender"]

@@ -55,6 +55,11 @@ def lib():
         "rtow_trace_counters": (C.c_int, [vp, vp, u64, C.c_int, P(C.c_double), P(C.c_double)]),
         "rtow_render_counters": (C.c_int, [vp, P(abi.Camera), P(abi.RenderParams), P(abi.WorkCounters)]),
         "rtow_render_profile": (C.c_int, [vp, P(abi.RenderProfile)]),
+        "rtow_multi_create": (C.c_int, [P(abi.SceneDesc), P(i32), i32, P(vp)]),
+        "rtow_multi_render": (C.c_int, [vp, P(abi.Camera), P(abi.RenderParams), vp, vp, P(abi.Stats)]),
+        "rtow_multi_device_count": (C.c_int, [vp]),
+        "rtow_multi_peer_mapped": (C.c_int, [vp]),
+        "rtow_multi_destroy": (None, [vp]),
         "rtow_last_error": (C.c_char_p, []),
         "rtow_build_info": (C.c_char_p, []),
         "rtow_host_scene_build": (C.c_int, [C.c_char_p, u64, C.c_int, C.c_int, P(vp)]),
@@ -80,6 +85,7 @@ def lib():
 EXPORTED_SYMBOLS = [
     "rtow_device_count", "rtow_scene_create", "rtow_scene_destroy", "rtow_trace_rays", "rtow_trace_rays_device",
     "rtow_render", "rtow_render_accumulate_device", "rtow_render_accumulate_device_noalloc", "rtow_render_accumulate_moments_device", "rtow_stream_stats", "rtow_resolve_device", "rtow_trace_counters", "rtow_render_counters", "rtow_render_profile",
+    "rtow_multi_create", "rtow_multi_render", "rtow_multi_device_count", "rtow_multi_peer_mapped", "rtow_multi_destroy",
     "rtow_last_error", "rtow_build_info", "rtow_host_scene_build", "rtow_host_scene_desc", "rtow_host_scene_free",
     "rtow_host_set_image", "rtow_host_set_image_dir", "rtow_host_decode_image", "rtow_host_free_image", "rtow_host_camera", "rtow_write_ppm", "rtow_write_pfm", "rtow_write_exr", "rtow_host_camera_oriented",
 ]
@@ -265,6 +271,46 @@ class DeviceScene:
 
     def resolve_device(self, d_accum_ptr, width, height, spp, d_rgb_ptr=None, d_bgra_ptr=None, stream=None):
         _check(lib().rtow_resolve_device(self._h, d_accum_ptr, width, height, spp, d_rgb_ptr, d_bgra_ptr, stream))
+
+
+class MultiDeviceScene:
+    """rtow_multi*: the scene on several GPUs of this box, one frame rendered by all of them (spp-sharded) from this process."""
+
+    def __init__(self, desc, devices=None):
+        L = lib()
+        h = C.c_void_p()
+        if devices is None:
+            _check(L.rtow_multi_create(C.byref(desc), None, 0, C.byref(h)))
+        else:
+            arr = (C.c_int32 * len(devices))(*devices)
+            _check(L.rtow_multi_create(C.byref(desc), arr, len(devices), C.byref(h)))
+        self._h = h
+        self.shards = L.rtow_multi_device_count(h)
+        self.peer_mapped = L.rtow_multi_peer_mapped(h)
+
+    def render(self, cam, params, want_bgra=False):
+        W, H = params.width, (params.row_count if params.row_count > 0 else params.height)
+        rgb = np.zeros((H, W, 3), dtype=np.float32)
+        bgra = np.zeros((H, W, 4), dtype=np.uint8) if want_bgra else None
+        st = abi.Stats()
+        _check(lib().rtow_multi_render(self._h, C.byref(cam), C.byref(params), rgb.ctypes.data, bgra.ctypes.data if want_bgra else None, C.byref(st)))
+        return (rgb, bgra, st) if want_bgra else (rgb, st)
+
+    def render_into(self, cam, params, rgb_out, bgra_out=None):
+        st = abi.Stats()
+        _check(lib().rtow_multi_render(self._h, C.byref(cam), C.byref(params), rgb_out, bgra_out, C.byref(st)))
+        return st
+
+    def close(self):
+        if self._h:
+            lib().rtow_multi_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def write_ppm(path, rgb):

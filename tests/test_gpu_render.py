@@ -312,3 +312,32 @@ def test_converged_image_matches_reference_golden(gpu, abi, kernel):
         assert 0.85 < z2 < 1.15, f"{name}: z2 = {z2}"
         assert flat < 1e-3 and rmse < 1.15 * expected
         assert abs(st.rays / st.paths - float(g["rays_per_path"])) < 0.01 * float(g["rays_per_path"])
+
+
+def test_multi_gpu_render_through_the_c_abi(gpu, abi, port):
+    """rtow_multi_render (one process, one host thread per shard, one reduce+resolve kernel over peer memory) equals the
+    1-device rtow_render up to fp32 summation order, and the oracle.  With one GPU on the box both shards share it; with
+    two or more the second shard sits on device 1 and is read over the peer mapping."""
+    ndev = gpu.lib().rtow_device_count()
+    host = gpu.HostScene("random_ned", seed=12345, wrap=True, image=earth_image())
+    W, H, spp = 128, 72, 12
+    cam = gpu.main_camera(W, H)
+    p = abi.default_render_params(W, H, spp, seed=19)
+    one, one_bgra, st1 = gpu.DeviceScene(host.desc).render(cam, p, want_bgra=True)
+    for devices in ([0, 1 % ndev], [0, 0, 1 % ndev], None):
+        m = gpu.MultiDeviceScene(host.desc, devices)
+        assert m.shards == (len(devices) if devices else ndev)
+        img, bgra, st = m.render(cam, p, want_bgra=True)
+        assert st.paths == W * H * spp and st.rays == st1.rays
+        assert np.abs(img - one).max() <= 2e-5 * max(1.0, float(one.max()))
+        assert (np.abs(bgra.astype(int) - one_bgra.astype(int)) <= 1).all() and (bgra != one_bgra).mean() < 1e-3
+        # a band of rows and a sample sub-range through the same entry
+        pb = abi.default_render_params(W, H, spp, seed=19, row_begin=16, row_count=24, sample_begin=2, sample_count=7)
+        band, _ = m.render(cam, pb)
+        want, _ = gpu.DeviceScene(host.desc).render(cam, pb)
+        assert band.shape == (24, W, 3) and np.abs(band - want).max() <= 2e-5 * max(1.0, float(want.max()))
+        m.close()
+    ref = port.render(host.desc, cam, p)["sum"] / np.float32(spp)
+    assert np.abs(img - ref).max() <= 2e-4 * max(1.0, float(ref.max()))
+    with pytest.raises(gpu.RtowError):
+        gpu.MultiDeviceScene(host.desc, [0, ndev + 3])
