@@ -222,9 +222,14 @@ def run_product(args):
     h_bgra = torch.empty(H, W, 4, dtype=torch.uint8).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev_t)   # > 126 MB L2
 
-    def barrier():
+    cpu_pg = dist.new_group(backend="gloo") if world > 1 else None
+
+    def barrier(on_cpu=False):
+        # on_cpu: the waiting ranks block in a gloo barrier on the host, so that no NCCL kernel spins on their GPUs while rank 0
+        # drives those GPUs itself (the N > 1 e2e leg)
         if world > 1:
-            dist.barrier()
+            torch.cuda.synchronize()
+            dist.barrier(group=cpu_pg) if on_cpu else dist.barrier()
         torch.cuda.synchronize()
 
     def step_resident():
@@ -235,26 +240,28 @@ def run_product(args):
         if rank == 0:
             scene.resolve_device(accum.data_ptr(), W, H, spp, rgb.data_ptr(), bgra.data_ptr(), sptr)
 
+    multi = None
+
     def step_e2e():
+        # the call a user of the library makes: host buffers in and out.  N > 1: rtow_multi_render from ONE process (rank 0 of
+        # this harness) drives all N GPUs -- one host thread per GPU, one reduce + resolve kernel over peer memory -- while the
+        # other ranks wait at the barrier with their GPUs idle
         if world == 1:
             scene.render_into(cam, full, h_rgb.data_ptr(), h_bgra.data_ptr())   # rtow_render: synchronous, host buffers
-        else:
-            step_resident()
-            if rank == 0:
-                h_rgb.copy_(rgb, non_blocking=True)
-                h_bgra.copy_(bgra, non_blocking=True)
+        elif rank == 0:
+            multi.render_into(cam, full, h_rgb.data_ptr(), h_bgra.data_ptr())   # rtow_multi_render: synchronous, host buffers
 
-    def timed(step, steps):
+    def timed(step, steps, on_cpu=False):
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
-        barrier()
+        barrier(on_cpu)
         t0 = time.time()
         for a, z in ev:
             flush.fill_(1)            # L2 flush between timed iterations (not timed)
-            barrier()
+            barrier(on_cpu)
             a.record(stream)
             step()
             z.record(stream)
-        barrier()
+        barrier(on_cpu)
         t1 = time.time()
         ms = torch.tensor([sum(a.elapsed_time(z) for a, z in ev)], dtype=torch.float64, device=dev_t)
         if world > 1:
@@ -274,10 +281,21 @@ def run_product(args):
         dist.all_reduce(rays_t, op=dist.ReduceOp.SUM)
     rays_per_step = float(rays_t.item())
 
+    if world > 1 and rank == 0:
+        multi = pkg.MultiDeviceScene(host.desc, list(range(world)))
     for _ in range(args.warmup):
         step_e2e()
     torch.cuda.synchronize()
-    ms_e2e, _, _ = timed(step_e2e, args.steps)
+    ms_e2e, _, _ = timed(step_e2e, args.steps, on_cpu=True)
+    e2e_api = "rtow_render" if world == 1 else f"rtow_multi_render over {world} devices from one process ({multi.peer_mapped if multi else 0} peer-mapped)"
+    if multi is not None:
+        multi.close()
+
+    # ---- the other render configs of BASELINE.json, same harness (all ranks take part) --------------------------
+    extra = {}
+    if not args.no_extra and (W, H, spp, args.scene) == (WIDTH, HEIGHT, SPP, SCENE):
+        for key, (sc_name, w2, h2, spp2, what) in EXTRA_CONFIGS.items():
+            extra[key] = render_block(pkg, abi, torch, dist, dev_t, stream, world, rank, local, sc_name, w2, h2, spp2, what, flush, args)
 
     if rank != 0:
         if world > 1:
@@ -366,7 +384,7 @@ def run_product(args):
         "mrays_per_s": rays_per_step / (ms_step * 1e-3) / 1e6,
         "rays_per_path": rays_per_path,
         "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": C.sizeof(abi.Camera) + C.sizeof(abi.RenderParams),
-                "d2h_bytes_per_step": W * H * 3 * 4 + W * H * 4, "ms_per_step": ms_e2e / args.steps},
+                "d2h_bytes_per_step": W * H * 3 * 4 + W * H * 4, "ms_per_step": ms_e2e / args.steps, "api": e2e_api},
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,
         "roofline": dict({"bound": "fp32_issue", "achieved": achieved_tops, "peak": peak_tops, "unit": "Tlaneop/s", "frac": achieved_tops / peak_tops,
@@ -378,12 +396,77 @@ def run_product(args):
         "roofline_hbm": {"bound": "hbm", "achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak, "traffic": traffic,
                          "algorithmic_bytes_per_launch": alg_bytes, "peak_source": hbm_src, "note": hbm_note},
         "bvh_hit": bvh,
+        "other_configs": extra,
         "cpu_baseline": cpu,
     }
     print(json.dumps(line), file=JSON_OUT, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+# BASELINE.json configs[2] and configs[3] beside the headline config: same harness, spp-sharded over the ranks.  The sample
+# counts are bounded so that the default run stays within minutes (Mpaths/s does not depend on spp beyond the ~5 ms of
+# per-frame fixed cost, which these counts already amortise); the full counts are 512 and 4096.
+EXTRA_CONFIGS = {
+    "configs[2]_textured": ("random_ned", 1920, 1080, 512, "configs[2]: textured scene (checker + Perlin noise + 2048x1024 JPEG earth image texture = randomScene_NED), 1920x1080, 512 spp"),
+    "configs[3]_cornell_smoke": ("cornell_smoke_ned", 3840, 2160, 128, "configs[3]: Cornell box with constantMedium smoke volumes, 3840x2160, 128 of the 4096 spp per step (bounded sample)"),
+}
+
+
+def render_block(pkg, abi, torch, dist, dev_t, stream, world, rank, local, scene_name, W, H, spp, what, flush, args):
+    host = pkg.HostScene(scene_name, seed=SCENE_SEED, wrap=True)
+    scene = pkg.DeviceScene(host.desc, device=local)
+    cam = pkg.main_camera(W, H)
+    b = spp * rank // world
+    n = spp * (rank + 1) // world - b
+    my = abi.default_render_params(W, H, spp, seed=RENDER_SEED, max_depth=DEPTH, sample_begin=b, sample_count=n)
+    accum = torch.zeros(H, W, 3, dtype=torch.float32, device=dev_t)
+    rgb = torch.empty(H, W, 3, dtype=torch.float32, device=dev_t)
+    bgra = torch.empty(H, W, 4, dtype=torch.uint8, device=dev_t)
+    sptr = stream.cuda_stream
+
+    def step():
+        accum.zero_()
+        scene.accumulate_device(cam, my, accum.data_ptr(), sptr)
+        if world > 1:
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            scene.resolve_device(accum.data_ptr(), W, H, spp, rgb.data_ptr(), bgra.data_ptr(), sptr)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    step()                                   # warm-up (allocations, first-touch)
+    steps = 2
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for a, z in ev:
+        flush.fill_(1)
+        barrier()
+        a.record(stream)
+        step()
+        z.record(stream)
+    barrier()
+    ms = torch.tensor([sum(a.elapsed_time(z) for a, z in ev)], dtype=torch.float64, device=dev_t)
+    st = scene.stream_stats(sptr)
+    rays = torch.tensor([float(st.rays)], dtype=torch.float64, device=dev_t)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(rays, op=dist.ReduceOp.SUM)
+    ms_step = float(ms.item()) / steps
+    paths = float(W) * H * spp
+    pr = scene.render_profile()
+    out = {"workload": what, "image_texture": describe_images(host.arrays()["images"], scene_name), "value": paths / (ms_step * 1e-3) / 1e6, "unit": "Mpaths/s",
+           "mrays_per_s": float(rays.item()) / (ms_step * 1e-3) / 1e6, "rays_per_path": float(rays.item()) / paths, "ms_per_step": ms_step, "steps": steps,
+           "n_gpus": world, "mean_radiance": float(rgb.mean().item()) if rank == 0 else None}
+    if pr.sampled_iterations:
+        out["extend_kernel_ms"] = pr.extend_ms_sum / pr.sampled_iterations
+        out["shade_kernel_ms"] = pr.shade_ms_sum / pr.sampled_iterations
+        out["pool_slots"] = pr.pool_slots
+    scene.close()
+    return out
 
 
 def bvh_hit_bench(pkg, abi, torch, dev_t, stream, args):
@@ -415,6 +498,20 @@ def bvh_hit_bench(pkg, abi, torch, dev_t, stream, args):
             torch.cuda.synchronize()
             ms = a.elapsed_time(z) / reps
             out[f"{name}_{tag}_mrays_per_s"] = len(rays) / (ms * 1e-3) / 1e6
+        # e2e: rtow_trace_rays with HOST buffers (pinned), the copies inside the timed region (CUDA events inside the call)
+        h_rays = torch.from_numpy(rays.view(np.uint8).reshape(len(rays), -1).copy()).pin_memory()
+        h_hits = torch.empty(len(rays), 48, dtype=torch.uint8).pin_memory()
+        best = None
+        for _ in range(3):
+            st = abi.Stats()
+            rc = pkg.lib().rtow_trace_rays(scene._h, h_rays.data_ptr(), len(rays), h_hits.data_ptr(), abi.TRAVERSE_FAST, 0, C.byref(st))
+            if rc != abi.OK:
+                raise RuntimeError(pkg.lib().rtow_last_error().decode())
+            best = st.total_ms if best is None else min(best, st.total_ms)
+        out[f"{name}_fast_e2e_mrays_per_s"] = len(rays) / (best * 1e-3) / 1e6
+        out[f"{name}_e2e_h2d_bytes"], out[f"{name}_e2e_d2h_bytes"] = int(h_rays.numel()), int(h_hits.numel())
+        assert bytes(h_hits[:4096].numpy().tobytes()) == bytes(d_hits[:4096].cpu().numpy().tobytes())
+        del h_rays, h_hits
         hits = d_hits.cpu().numpy().view(abi.hit_dtype).reshape(-1)
         out[f"{name}_hit_fraction"] = float((hits["prim_id"] >= 0).mean())
         nv, pt = scene.trace_counters(rays[:: len(rays) >> 18], traverse=abi.TRAVERSE_FAST)    # every 64th ray: the whole frustum, not its first rows
@@ -476,6 +573,7 @@ def main():
     ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 megakernel, 2 wavefront")
     ap.add_argument("--no-bvh", action="store_true", help="skip the config-5 BVH hit-test figures")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the configs[2] / configs[3] blocks")
     ap.add_argument("--bvh-spheres", type=int, default=1000000)
     ap.add_argument("--bvh-skip-exact", action="store_true")
     args = ap.parse_args()
