@@ -279,7 +279,7 @@ int rtow_render_accumulate_device(rtow_scene *scene, const rtow_camera *cam,
  * Synchronises `stream` before returning, like the allocating entry.  params->kernel = RTOW_KERNEL_MEGA is refused. */
 #define RTOW_NOALLOC_MAX_POOL 65536
 #define RTOW_NOALLOC_MAX_PIXELS 262144
-#define RTOW_NOALLOC_SCRATCH_BYTES (RTOW_NOALLOC_MAX_POOL * 32 * 2 + RTOW_NOALLOC_MAX_POOL * 16 * 4 + RTOW_NOALLOC_MAX_PIXELS * 3 * 8 + 512)
+#define RTOW_NOALLOC_SCRATCH_BYTES (RTOW_NOALLOC_MAX_POOL * 32 * 4 + RTOW_NOALLOC_MAX_POOL * 16 * 4 + RTOW_NOALLOC_MAX_PIXELS * 3 * 8 + 512)
 int rtow_render_accumulate_device_noalloc(rtow_scene *scene, const rtow_camera *cam,
                                           const rtow_render_params *params, float *d_accum, void *stream);
 
@@ -333,13 +333,18 @@ int rtow_render_counters(rtow_scene *scene, const rtow_camera *cam, const rtow_r
                          rtow_work_counters *out);
 
 /* Per-kernel timing of the last accumulate/render call on this scene (wavefront path): CUDA events around the
- * extend and shade launches of every 8th bounce iteration that ran on a full pool.  Used by bench.py's roofline. */
+ * extend and shade launches of the bounce iterations that precede a host poll and ran on a full pool.  Used by
+ * bench.py's roofline. */
 typedef struct rtow_render_profile_t {
     int32_t kernel;                 /* RTOW_KERNEL_MEGA or RTOW_KERNEL_WAVEFRONT: what actually ran */
     uint32_t iterations;            /* bounce iterations (extend + shade launch pairs) */
     uint32_t pool_slots;            /* path slots = rays per full-pool extend launch */
     uint32_t sampled_iterations;
     float extend_ms_sum, shade_ms_sum;   /* over the sampled iterations */
+    uint32_t tail_iterations;       /* bounce iterations after the last work item was handed out (the drain of the stream) */
+    uint32_t polls;                 /* host synchronisations that looked at the device's progress counters */
+    float tail_ms;                  /* device time from the poll that first saw the work exhausted to the end of the drain */
+    uint32_t reserved;
 } rtow_render_profile_t;
 int rtow_render_profile(rtow_scene *scene, rtow_render_profile_t *out);
 

@@ -135,6 +135,10 @@ class RenderProfile(C.Structure):
         ("sampled_iterations", C.c_uint32),
         ("extend_ms_sum", C.c_float),
         ("shade_ms_sum", C.c_float),
+        ("tail_iterations", C.c_uint32),
+        ("polls", C.c_uint32),
+        ("tail_ms", C.c_float),
+        ("reserved", C.c_uint32),
     ]
 
 

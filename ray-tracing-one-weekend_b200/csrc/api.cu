@@ -204,13 +204,15 @@ int ensure_image_buffers(rtow_scene *s, size_t pixels) {
 
 int ensure_wavefront(rtow_scene *s, int pool, size_t pixels) {
     if (pool <= s->wf_pool && pixels <= s->wf_pixels) return RTOW_OK;
+    pool = std::max(pool, s->wf_pool); pixels = std::max(pixels, s->wf_pixels);      // capacity only grows (bands, previews)
     for (void *p : s->wf_allocs) cudaFree(p);
     s->wf_allocs.clear(); s->wf_pool = 0; s->wf_pixels = 0;
-    pool = std::max(pool, s->wf_pool); pixels = std::max(pixels, s->wf_pixels);
     auto grab = [&](void **p, size_t bytes) { cudaError_t e = cudaMalloc(p, bytes); if (e == cudaSuccess) s->wf_allocs.push_back(*p); return e; };
     WavefrontLaunch &W = s->wf;
-    CUDA_TRY(grab((void **)&W.ray, (size_t)pool * 32));
-    CUDA_TRY(grab((void **)&W.idh, (size_t)pool * 32));
+    for (int b = 0; b < 2; ++b) {
+        CUDA_TRY(grab((void **)&W.ray_buf[b], (size_t)pool * 32));
+        CUDA_TRY(grab((void **)&W.idh_buf[b], (size_t)pool * 32));
+    }
     CUDA_TRY(grab((void **)&W.queue, (size_t)pool * RTOW_WF_MAX_CLASSES * 4));
     CUDA_TRY(grab((void **)&W.counts, 2 * RTOW_WF_MAX_CLASSES * 4));
     CUDA_TRY(grab((void **)&W.fixed, pixels * 3 * 8));
@@ -260,12 +262,12 @@ int check_render_args(const rtow_scene *s, const rtow_camera *cam, const rtow_re
 // ---- scratch of rtow_render_accumulate_device_noalloc -------------------------------------------------------------
 // The wavefront path's work memory (path pool, class queues, fixed-point pixel sums, control words) in ONE file-scope
 // device array, so that the entry point below allocates nothing.  Every GPU that loads the library holds these
-// RTOW_NOALLOC_SCRATCH_BYTES (~14 MB) until the process exits.  In host code `g_noalloc_scratch` is only a stand-in for the
+// RTOW_NOALLOC_SCRATCH_BYTES (~18 MB) until the process exits.  In host code `g_noalloc_scratch` is only a stand-in for the
 // symbol, not a device address: the address comes from cudaGetSymbolAddress, once per device, with that device current.
 constexpr size_t NA_POOL = RTOW_NOALLOC_MAX_POOL, NA_PIXELS = RTOW_NOALLOC_MAX_PIXELS;
-constexpr size_t NA_OFF_RAY = 0;
-constexpr size_t NA_OFF_IDH = NA_OFF_RAY + NA_POOL * 32;
-constexpr size_t NA_OFF_QUEUE = NA_OFF_IDH + NA_POOL * 32;
+constexpr size_t NA_OFF_RAY = 0;                                   // two buffers of each (wavefront.cu: in / out)
+constexpr size_t NA_OFF_IDH = NA_OFF_RAY + 2 * NA_POOL * 32;
+constexpr size_t NA_OFF_QUEUE = NA_OFF_IDH + 2 * NA_POOL * 32;
 constexpr size_t NA_OFF_FIXED = NA_OFF_QUEUE + NA_POOL * RTOW_WF_MAX_CLASSES * 4;
 constexpr size_t NA_OFF_COUNTS = NA_OFF_FIXED + NA_PIXELS * 3 * 8;
 constexpr size_t NA_OFF_CONTROL = NA_OFF_COUNTS + 256;
@@ -313,13 +315,16 @@ int rtow_render_accumulate_device_noalloc(rtow_scene *s, const rtow_camera *cam,
     WavefrontLaunch W;
     std::memset(&W, 0, sizeof W);
     W.L = L; W.pool = (int)pool; W.total_items = items;
-    W.ray = (float4 *)(base + NA_OFF_RAY); W.idh = (int4 *)(base + NA_OFF_IDH);
+    for (int b = 0; b < 2; ++b) {
+        W.ray_buf[b] = (float4 *)(base + NA_OFF_RAY + b * NA_POOL * 32);
+        W.idh_buf[b] = (int4 *)(base + NA_OFF_IDH + b * NA_POOL * 32);
+    }
     W.queue = (int *)(base + NA_OFF_QUEUE); W.counts = (unsigned *)(base + NA_OFF_COUNTS);
     W.fixed = (unsigned long long *)(base + NA_OFF_FIXED); W.fixed_sq = nullptr;
     W.control = (unsigned long long *)(base + NA_OFF_CONTROL);
     W.next_item = W.control; W.dead_slots = W.control + 1; W.extend_head = W.control + 2; W.stats = W.control + 3;
     // The array keeps the previous call's contents: run_wavefront clears what must start at zero (pixel sums, control words,
-    // queue lengths) and wf_generate_kernel rewrites every slot of the pool it uses; stale slots and queue entries beyond
+    // queue lengths) and wf_generate_kernel rewrites every entry of the pool it uses; stale entries and queue slots beyond
     // are never read.  Its progress polls land in a local (pageable) word: no pinned allocation either.
     unsigned long long polled[2] = {0ull, 0ull};
     CUDA_TRY(run_wavefront(s->d, *cam, W, d_accum, nullptr, polled, (cudaStream_t)stream, nullptr, nullptr));
@@ -677,6 +682,7 @@ int rtow_render_profile(rtow_scene *s, rtow_render_profile_t *out) {
     if (s->pending_wavefront) {
         out->iterations = s->wf_prof.iterations; out->pool_slots = s->wf_prof.pool; out->sampled_iterations = s->wf_prof.samples;
         out->extend_ms_sum = s->wf_prof.extend_ms; out->shade_ms_sum = s->wf_prof.shade_ms;
+        out->tail_iterations = s->wf_prof.tail_iterations; out->polls = s->wf_prof.polls; out->tail_ms = s->wf_prof.tail_ms;
     }
     return RTOW_OK;
 }

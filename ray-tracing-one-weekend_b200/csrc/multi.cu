@@ -125,6 +125,7 @@ void rtow_multi_destroy(rtow_multi *m) {
     cudaSetDevice(m->devices[0]);
     if (m->t0) cudaEventDestroy(m->t0);
     if (m->t1) cudaEventDestroy(m->t1);
+    cudaGetLastError();         // tear-down must not leave an error behind for the next call to trip over
     delete m;
 }
 
@@ -134,14 +135,14 @@ int rtow_multi_create(const rtow_scene_desc *desc, const int32_t *devices, int32
     const int visible = rtow_device_count();
     if (visible == 0) return set_error(RTOW_ERR_NO_DEVICE, "no CUDA device visible (this library has no CPU path)");
     if (n_devices > RTOW_MULTI_MAX) return set_error(RTOW_ERR_INVALID_ARG, "rtow_multi_create: at most 16 shards");
+    for (int k = 0; k < n_devices; ++k)
+        if (devices[k] < 0 || devices[k] >= visible) return set_error(RTOW_ERR_INVALID_ARG, "rtow_multi_create: device index out of range");
     rtow_multi *m = new rtow_multi;
     std::memset(m->scenes, 0, sizeof m->scenes); std::memset(m->streams, 0, sizeof m->streams); std::memset(m->done, 0, sizeof m->done);
     std::memset(m->accum, 0, sizeof m->accum); std::memset(m->staged, 0, sizeof m->staged);
     m->n = n_devices > 0 ? n_devices : (visible < RTOW_MULTI_MAX ? visible : RTOW_MULTI_MAX);      // n_devices <= 0: every visible device
     for (int k = 0; k < m->n; ++k) m->devices[k] = n_devices > 0 ? devices[k] : k;
     struct Guard { rtow_multi *m; ~Guard() { if (m) rtow_multi_destroy(m); } } guard{m};
-    for (int k = 0; k < m->n; ++k)
-        if (m->devices[k] < 0 || m->devices[k] >= visible) return set_error(RTOW_ERR_INVALID_ARG, "rtow_multi_create: device index out of range");
     for (int k = 0; k < m->n; ++k) {
         // one scene copy per shard (a device listed twice gets two: its shards then share the GPU, which is how a
         // single-GPU box exercises this path)

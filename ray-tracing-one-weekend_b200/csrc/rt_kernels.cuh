@@ -35,13 +35,22 @@ struct WavefrontLaunch {
     RenderLaunch L;
     int pool;                             // path slots (multiple of 256)
     unsigned long long total_items;       // work items = pixel groups of 32 x samples (incl. padding pixels)
-    // per-slot state (SoA in HBM): two arrays of 32-byte elements (two 16-byte halves each), so that the shade kernel --
-    // which reaches its slot through a queue, one scattered line per lane -- moves a slot with two 256-bit loads and stores.
-    // 64 bytes per path, no padding: the throughput T sits in the three words the ray and the ids leave free.
-    float4 *ray;                          // [2*slot] {o.xyz, time}  [2*slot+1] {d.xyz, T.x}
-    int4 *idh;                            // [2*slot] {pixel, sample, next Philox draw, depth}; depth < 0: the slot is dead
-                                          // [2*slot+1] {t bits, prim id (< 0: miss)} written by the extend kernel, {T.y, T.z}
-    int *queue;                           // RTOW_WF_MAX_CLASSES x pool slot indices, by shading class
+    // geometry of the work-item order (wf_item_to_pixel), filled by run_wavefront
+    unsigned long long block_items;       // padded pixels x 64: items per block of 64 sample indices
+    unsigned long long full_items;        // items in the full blocks
+    double inv_block_items;
+    unsigned full_blocks;
+    // per-entry path state (SoA in HBM): two arrays of 32-byte elements (two 16-byte halves each), moved with 256-bit loads
+    // and stores.  64 bytes per path, no padding: the throughput T sits in the three words the ray and the ids leave free.
+    // Two buffers used in turn: bounce i is traced and shaded out of `in`, its successors are written densely to `out`.
+    //   ray [2*e] {o.xyz, time}  [2*e+1] {d.xyz, T.x}      (T.x == WF_DEAD_BITS: the entry is dead)
+    //   idh [2*e] {pixel, sample, next Philox draw, depth}  (depth < 0: dead)
+    //       [2*e+1] {t bits, prim id (< 0: miss)} written by the extend kernel, {T.y, T.z}
+    float4 *ray_buf[2];
+    int4 *idh_buf[2];
+    float4 *ray_in, *ray_out;
+    int4 *idh_in, *idh_out;
+    int *queue;                           // RTOW_WF_MAX_CLASSES x pool entry indices of `in`, by shading class
     unsigned *counts;                     // 2 x RTOW_WF_MAX_CLASSES queue lengths (double-buffered by bounce parity)
     unsigned long long *fixed;            // W*H*3 radiance sums, Q31.32
     unsigned long long *fixed_sq;         // W*H*3 sums of squared per-sample radiance, Q43.20; null unless moments were asked for
@@ -52,6 +61,9 @@ struct WavefrontLaunch {
 struct WavefrontProfile {
     float extend_ms = 0.f, shade_ms = 0.f;
     uint32_t samples = 0, iterations = 0, pool = 0;
+    uint32_t tail_iterations = 0;         // bounce iterations after the last work item was handed out (the drain)
+    uint32_t polls = 0;                   // host synchronisations that looked at the device's progress counters
+    float tail_ms = 0.f;                  // device time of the drain (first poll that saw the work exhausted -> end)
 };
 cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaunch &W, float *d_accum, float *d_accum_sq, unsigned long long *h_pinned,
                           cudaStream_t stream, uint32_t *launches_out, WavefrontProfile *prof);

@@ -1,15 +1,19 @@
-// wavefront.cu -- RTOW_KERNEL_WAVEFRONT: the pixel/sample loop + color() (main.cpp:932-956, color.h:12-59) as a pool
-// of path states in HBM advanced by two kernels per bounce:
+// wavefront.cu -- RTOW_KERNEL_WAVEFRONT: the pixel/sample loop + color() (main.cpp:932-956, color.h:12-59) as a stream of
+// path states in HBM advanced by two kernels per bounce.  The states live in two buffers used in turn: bounce i is traced
+// and shaded out of buffer `in`, and its successors are written, densely, to buffer `out`.
 //
-//   wf_extend_kernel   world->hit() for every live slot: the persistent, vote-scheduled closest-hit traversal of
-//                      kernels.cu (lanes refill from a global counter), writes {t, prim} and appends the slot to the
-//                      queue of its shading class (miss / material x root texture) with warp-aggregated atomics
-//   wf_shade_kernel    one thread per queued slot, queues laid out class after class so that a warp shades one class:
-//                      emitted + scatter (material.h), textures / Perlin (texture.h, noise.h), sky on a miss; a path
-//                      that ends adds its radiance to the pixel (64-bit fixed point: order-independent, so the image
-//                      is deterministic although slots are handed out dynamically) and the slot starts the next
-//                      (pixel, sample) work item from a global counter (camera.h:123-135) -- no separate generate pass
-//                      after the first
+//   extend             world->hit() for entries [0, n) of `in` (n = the previous bounce's queue total), writes {t, prim} and
+//                      appends the entry to the queue of its shading class (miss / material x root texture) with
+//                      warp-aggregated atomics.  wf_extend_kernel: persistent, vote-scheduled traversal of the 4-wide BVH;
+//                      wf_extend_exact_kernel: the reference walk (list scenes, EXACT traversal)
+//   wf_shade_kernel    thread j shades queue entry j (queues laid out class after class so that a warp shades one class):
+//                      emitted + scatter (material.h), textures / Perlin (texture.h, noise.h), sky on a miss, and writes the
+//                      path's next ray to out[j] -- coalesced, and sorted by the class of the surface it leaves: a warp of
+//                      camera-ray misses leaves the new camera rays of 32 neighbouring pixels side by side, so the next
+//                      extend pass traverses them as one coherent packet.  A path that ends adds its radiance to the pixel
+//                      (64-bit fixed point: order-independent, so the image is deterministic) and out[j] starts the next
+//                      (pixel, sample) work item from a global counter (camera.h:123-135); when the work runs out, out[j]
+//                      is marked dead, dead entries are never queued, and the stream shrinks by itself
 //   wf_finalize_kernel fixed-point sums -> += the caller's fp32 accumulators
 //
 // Path arithmetic is the megakernel's, instruction for instruction (same headers), and the Philox stream of a path is
@@ -43,6 +47,10 @@ __device__ __forceinline__ void st256(void *p, const float4 &a, const float4 &b)
                  :: "l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w) : "memory");
 }
 
+// A dead entry carries this bit pattern in the throughput word of its ray record (a NaN no arithmetic produces: computed
+// NaNs are 0x7fffffff), so the extend kernels decide "dead" from the 32 bytes they load anyway; the ids keep depth = -1 too.
+#define WF_DEAD_BITS ((int)0xffffdead)
+
 #define WF_SAMPLE_BLOCK 64
 __device__ __forceinline__ void wf_item_to_pixel(const WavefrontLaunch &W, unsigned long long item, int &pixel, int &sample) {
     // Order of the work items: blocks of WF_SAMPLE_BLOCK sample indices; inside a block, groups of 32 neighbouring
@@ -51,25 +59,30 @@ __device__ __forceinline__ void wf_item_to_pixel(const WavefrontLaunch &W, unsig
     // samples each.  Measured (B200, shade kernel per 2^20 slots): 0.085 ms this way; 0.125 ms with all pixels of one
     // sample in flight (the 64-bit pixel atomics then sweep 25 MB of accumulators); 0.135 ms with 1024 samples of only
     // 1024 pixels in flight (the atomics collide).
-    const unsigned long long padded = ((unsigned long long)W.L.pixel_count + 31ull) & ~31ull;      // pixels of this launch's band
-    const unsigned long long full_blocks = (unsigned)W.L.sample_count / WF_SAMPLE_BLOCK;
-    const unsigned long long full_items = full_blocks * padded * WF_SAMPLE_BLOCK;
-    unsigned long long j = item, first = 0, bsz = WF_SAMPLE_BLOCK;
-    if (item < full_items) {
-        const unsigned long long sb = item / (padded * WF_SAMPLE_BLOCK);
-        j = item - sb * (padded * WF_SAMPLE_BLOCK);
-        first = sb * WF_SAMPLE_BLOCK;
-    } else {
-        j = item - full_items;
-        first = full_blocks * WF_SAMPLE_BLOCK;
-        bsz = (unsigned)W.L.sample_count - first;      // the last, partial block (>= 1 here)
+    // (a 64-bit integer division is ~100 instructions and every new path paid for two: the first is now a double multiply
+    // by the host's reciprocal with a one-step correction -- item counts stay far below 2^53 --, the second a shift in the
+    // full blocks of 64 samples)
+    const unsigned long long block_items = W.block_items;          // padded pixels of this launch's band x WF_SAMPLE_BLOCK
+    if (item < W.full_items) {
+        unsigned long long sb = (unsigned long long)__double2ll_rd((double)item * W.inv_block_items);
+        unsigned long long j = item - sb * block_items;
+        if ((long long)j < 0) { j += block_items; --sb; } else if (j >= block_items) { j -= block_items; ++sb; }
+        pixel = (int)((j >> 11) * 32ull + (j & 31ull));            // groups of 32 pixels x 64 samples = 2048 items
+        sample = (int)(sb * WF_SAMPLE_BLOCK + ((j & 2047ull) >> 5));
+        return;
     }
-    const unsigned long long g = j / (32ull * bsz), k = j - g * (32ull * bsz);
-    pixel = (int)(g * 32ull + (k & 31ull));
+    const unsigned long long j = item - W.full_items;
+    const unsigned first = W.full_blocks * WF_SAMPLE_BLOCK;
+    const unsigned per_group = 32u * ((unsigned)W.L.sample_count - first);      // the last, partial block (>= 1 sample here)
+    unsigned long long g;
+    unsigned k;
+    if (j < (1ull << 32)) { g = (unsigned)j / per_group; k = (unsigned)j - (unsigned)g * per_group; }
+    else { g = j / per_group; k = (unsigned)(j - g * per_group); }
+    pixel = (int)(g * 32ull + (k & 31u));
     sample = (int)(first + (k >> 5));
 }
 
-// Starts the path of work item `item` in `slot` (main.cpp:943-948).  Returns false for the padding pixels of the last group.
+// Starts the path of work item `item` in entry `slot` of the out buffer (main.cpp:943-948).  Returns false for the padding pixels of the last group.
 __device__ __forceinline__ bool wf_start_path(const WavefrontLaunch &W, const rtow_camera &cam, unsigned long long item, int slot) {
     int pixel, s;
     wf_item_to_pixel(W, item, pixel, s);
@@ -84,8 +97,8 @@ __device__ __forceinline__ bool wf_start_path(const WavefrontLaunch &W, const rt
     float v = (float)((double)row + (double)jv) / (float)W.L.height;
     Ray r;
     camera_ray(cam, u, v, g, r);
-    st256(W.ray + 2 * (size_t)slot, make_float4(r.ox, r.oy, r.oz, r.time), make_float4(r.dx, r.dy, r.dz, 1.f));
-    st256(W.idh + 2 * (size_t)slot, make_float4(__int_as_float(pixel), __int_as_float(W.L.sample_begin + s), __int_as_float((int)g.next), __int_as_float(0)),
+    st256(W.ray_out + 2 * (size_t)slot, make_float4(r.ox, r.oy, r.oz, r.time), make_float4(r.dx, r.dy, r.dz, 1.f));
+    st256(W.idh_out + 2 * (size_t)slot, make_float4(__int_as_float(pixel), __int_as_float(W.L.sample_begin + s), __int_as_float((int)g.next), __int_as_float(0)),
           make_float4(0.f, __int_as_float(-1), 1.f, 1.f));
     return true;
 }
@@ -120,14 +133,40 @@ __device__ __forceinline__ void wf_refill(const WavefrontLaunch &W, const rtow_c
         }
     }
     const unsigned dm = __ballot_sync(full, dead);
-    if (dead) W.idh[2 * (size_t)slot].w = -1;
+    if (dead) {
+        W.idh_out[2 * (size_t)slot].w = -1;
+        W.ray_out[2 * (size_t)slot + 1].w = __int_as_float(WF_DEAD_BITS);
+    }
     if (lane == 0 && dm) atomicAdd(W.dead_slots, (unsigned long long)__popc(dm));
 }
 
 __global__ void __launch_bounds__(256) wf_generate_kernel(WavefrontLaunch W, rtow_camera cam) {
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;     // the grid covers the pool exactly (pool % 256 == 0)
+    if (slot == 0) W.counts[RTOW_WF_MAX_CLASSES] = (unsigned)W.pool;      // the "previous bounce's queue total" that bounce 0 reads
     bool dead;
     wf_refill(W, cam, true, slot, dead);
+}
+
+// entries of the bounce being traced = the total of the previous bounce's class queues (all 32 lanes call)
+__device__ __forceinline__ unsigned wf_entries(const WavefrontLaunch &W, int parity) {
+    const int lane = threadIdx.x & 31;
+    unsigned v = lane < RTOW_WF_MAX_CLASSES ? W.counts[(parity ^ 1) * RTOW_WF_MAX_CLASSES + lane] : 0u;
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// place of a traced entry in the queue of its shading class (all 32 lanes call; cls < 0: nothing to queue)
+__device__ __forceinline__ void wf_enqueue(const WavefrontLaunch &W, unsigned *counts, int cls, int slot) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned same = __match_any_sync(full, cls);
+    if (cls >= 0) {
+        const int leader = __ffs(same) - 1;
+        unsigned base = 0;
+        if (lane == leader) base = atomicAdd(&counts[cls], (unsigned)__popc(same));
+        base = __shfl_sync(same, base, leader);
+        W.queue[(size_t)cls * W.pool + base + __popc(same & ((1u << lane) - 1u))] = slot;
+    }
 }
 
 // ---- extend ------------------------------------------------------------------------------------------------
@@ -143,17 +182,18 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
     int slot = 0;
     bool has_ray = false, more = true;
     unsigned rays = 0;
-    // the path's Philox key, read back from the slot when a medium asks for it (rare) instead of living in three registers
+    // the path's Philox key, read back from the entry when a medium asks for it (rare) instead of living in three registers
     const auto key_of = [&] {
-        const int4 id = W.idh[2 * (size_t)slot];
+        const int4 id = W.idh_in[2 * (size_t)slot];
         RngKey k; k.seed = W.L.seed; k.pixel = (uint32_t)id.x; k.sample = (uint32_t)id.y; k.bounce = (uint32_t)id.w;
         return k;
     };
     unsigned *counts = W.counts + parity * RTOW_WF_MAX_CLASSES;
     const bool use_fast = W.L.traverse == RTOW_TRAVERSE_FAST && S.fast_nodes != nullptr;
+    const unsigned long long n = wf_entries(W, parity);
 
     for (;;) {
-        // 1. finished lanes: write {t, prim} and queue the slot under its shading class
+        // 1. finished lanes: write {t, prim} and queue the entry under its shading class
         {
             const bool fin = has_ray && T.cur == RTOW_TRAV_DONE;
             if (__any_sync(full, fin)) {
@@ -161,34 +201,28 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
                 if (fin) {
                     float t = 0.f; int pid = -1;
                     if (!fast_result(S, T, t, pid)) pid = -1;
-                    *reinterpret_cast<float2 *>(W.idh + 2 * (size_t)slot + 1) = make_float2(t, __int_as_float(pid));
+                    *reinterpret_cast<float2 *>(W.idh_in + 2 * (size_t)slot + 1) = make_float2(t, __int_as_float(pid));
                     cls = pid >= 0 ? __ldg(&S.prim_class[pid]) : 0;
                     has_ray = false;
                 }
-                const unsigned same = __match_any_sync(full, cls);
-                if (cls >= 0) {
-                    const int leader = __ffs(same) - 1;
-                    unsigned base = 0;
-                    if (lane == leader) base = atomicAdd(&counts[cls], (unsigned)__popc(same));
-                    base = __shfl_sync(same, base, leader);
-                    W.queue[(size_t)cls * W.pool + base + __popc(same & ((1u << lane) - 1u))] = slot;
-                }
+                wf_enqueue(W, counts, cls, slot);
             }
         }
-        // 2. idle lanes take the next slots of the pool; dead slots are skipped
+        // 2. idle lanes take the next entries of the stream (32 consecutive ones for a whole warp: they were written side by
+        //    side by one shade warp, i.e. they left the same class of surface -- camera rays of neighbouring pixels above all);
+        //    dead entries are skipped
         if (more) {
             const unsigned need = __ballot_sync(full, !has_ray);
             unsigned long long base = 0;
             if (lane == 0) base = atomicAdd(W.extend_head, (unsigned long long)__popc(need));
             base = __shfl_sync(full, base, 0);
-            if (base + __popc(need) >= (unsigned long long)W.pool) more = false;
+            if (base + __popc(need) >= n) more = false;
             if (!has_ray) {
                 const unsigned long long mine = base + __popc(need & ((1u << lane) - 1u));
-                if (mine < (unsigned long long)W.pool) {
-                    const int4 id = W.idh[2 * mine];
+                if (mine < n) {
                     float4 a, b;
-                    ld256(W.ray + 2 * mine, a, b);        // with the ids, not after them: one load latency, not two
-                    if (id.w >= 0) {
+                    ld256(W.ray_in + 2 * mine, a, b);
+                    if (__float_as_int(b.w) != WF_DEAD_BITS) {
                         slot = (int)mine; has_ray = true; rays++;
                         Ray r;
                         r.ox = a.x; r.oy = a.y; r.oz = a.z; r.time = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z;
@@ -196,7 +230,8 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
                         if (use_fast && fast_covers(S, r, 0.001f, FLT_MAX) && !(debug_exact_every && mine % (unsigned)debug_exact_every == 0)) {
                             fast_begin(S, r, 0.001f, FLT_MAX, T);
                         } else {
-                            // list scenes (nothing to cull) and rays outside the culling argument: the reference walk
+                            // rays outside the culling argument: the reference walk
+                            const int4 id = W.idh_in[2 * mine];
                             Rng g;
                             rng_init(g, W.L.seed, (uint32_t)id.x, (uint32_t)id.y);
                             g.bounce = (uint32_t)id.w;
@@ -231,41 +266,40 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
 
 // ---- extend, reference walk -----------------------------------------------------------------------------------
 // List scenes (a HitableList world has nothing to cull) and EXACT traversal: every ray walks the reference structure as is
-// (hitableList.h:20-38 / bvhNode.h:66-96).  No traversal state to keep, so this is the plain form -- one slot per thread,
-// no shared-memory stack -- and the primitive code gets the registers (wf_extend_kernel at 64 registers spilled 750 bytes
-// of its unused FastTrav around every call).
+// (hitableList.h:20-38 / bvhNode.h:66-96).  No traversal state to keep, so this is the plain form -- one entry per thread,
+// no shared-memory stack -- and the primitive code gets the registers.
 template <int MINB>
 __global__ void __launch_bounds__(128, MINB) wf_extend_exact_kernel(DScene S, WavefrontLaunch W, int parity) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    const size_t slot = (size_t)blockIdx.x * blockDim.x + threadIdx.x;      // the grid covers the pool exactly (pool % 256 == 0)
     unsigned *counts = W.counts + parity * RTOW_WF_MAX_CLASSES;
-    const int4 id = W.idh[2 * slot];
-    float4 a, b;
-    ld256(W.ray + 2 * slot, a, b);
-    int cls = -1;
-    if (id.w >= 0) {
-        Ray r;
-        r.ox = a.x; r.oy = a.y; r.oz = a.z; r.time = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z;
-        root_ray(S, r);
-        Rng g;
-        rng_init(g, W.L.seed, (uint32_t)id.x, (uint32_t)id.y);
-        g.bounce = (uint32_t)id.w;
-        float t = 0.f; int pid = -1; unsigned nv = 0, pt = 0;
-        if (!closest_hit_exact<false>(S, r, 0.001f, FLT_MAX, &g, t, pid, nv, pt)) { t = 0.f; pid = -1; }
-        *reinterpret_cast<float2 *>(W.idh + 2 * slot + 1) = make_float2(t, __int_as_float(pid));
-        cls = pid >= 0 ? __ldg(&S.prim_class[pid]) : 0;
+    const unsigned n = wf_entries(W, parity);
+    unsigned rays = 0;
+    for (unsigned tile = blockIdx.x; (unsigned long long)tile * 128u < n; tile += gridDim.x) {
+        const size_t slot = (size_t)tile * 128u + threadIdx.x;
+        int cls = -1;
+        if (slot < n) {
+            float4 a, b;
+            ld256(W.ray_in + 2 * slot, a, b);
+            if (__float_as_int(b.w) != WF_DEAD_BITS) {
+                const int4 id = W.idh_in[2 * slot];
+                Ray r;
+                r.ox = a.x; r.oy = a.y; r.oz = a.z; r.time = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z;
+                root_ray(S, r);
+                Rng g;
+                rng_init(g, W.L.seed, (uint32_t)id.x, (uint32_t)id.y);
+                g.bounce = (uint32_t)id.w;
+                float t = 0.f; int pid = -1; unsigned nv = 0, pt = 0;
+                if (!closest_hit_exact<false>(S, r, 0.001f, FLT_MAX, &g, t, pid, nv, pt)) { t = 0.f; pid = -1; }
+                *reinterpret_cast<float2 *>(W.idh_in + 2 * slot + 1) = make_float2(t, __int_as_float(pid));
+                cls = pid >= 0 ? __ldg(&S.prim_class[pid]) : 0;
+                rays++;
+            }
+        }
+        wf_enqueue(W, counts, cls, (int)slot);
     }
-    const unsigned same = __match_any_sync(full, cls);
-    if (cls >= 0) {
-        const int leader = __ffs(same) - 1;
-        unsigned base = 0;
-        if (lane == leader) base = atomicAdd(&counts[cls], (unsigned)__popc(same));
-        base = __shfl_sync(same, base, leader);
-        W.queue[(size_t)cls * W.pool + base + __popc(same & ((1u << lane) - 1u))] = (int)slot;
-    }
-    const unsigned live = __ballot_sync(full, cls >= 0);
-    if (lane == 0 && live) atomicAdd(&W.stats[0], (unsigned long long)__popc(live));
+    for (int off = 16; off; off >>= 1) rays += __shfl_down_sync(full, rays, off);
+    if (lane == 0 && rays) atomicAdd(&W.stats[0], (unsigned long long)rays);
 }
 
 // ---- shade -------------------------------------------------------------------------------------------------
@@ -325,8 +359,8 @@ __global__ void __launch_bounds__(256, 4) wf_shade_kernel(DScene S, WavefrontLau
     float Lr[3] = {0.f, 0.f, 0.f};
     if (valid) {
         float4 a, b, idf, hf;
-        ld256(W.ray + 2 * (size_t)slot, a, b);
-        ld256(W.idh + 2 * (size_t)slot, idf, hf);
+        ld256(W.ray_in + 2 * (size_t)slot, a, b);
+        ld256(W.idh_in + 2 * (size_t)slot, idf, hf);
         const int4 id = make_int4(__float_as_int(idf.x), __float_as_int(idf.y), __float_as_int(idf.z), __float_as_int(idf.w));
         const float2 hr = make_float2(hf.x, hf.y);
         // The path's throughput T rides in the three spare words of the two state elements.  Its radiance so far needs no
@@ -369,8 +403,8 @@ __global__ void __launch_bounds__(256, 4) wf_shade_kernel(DScene S, WavefrontLau
                 Lr[0] += T[0] * em[0]; Lr[1] += T[1] * em[1]; Lr[2] += T[2] * em[2];
                 if (go) {
                     T[0] *= atten[0]; T[1] *= atten[1]; T[2] *= atten[2];
-                    st256(W.ray + 2 * (size_t)slot, make_float4(h.p[0], h.p[1], h.p[2], stime), make_float4(sd[0], sd[1], sd[2], T[0]));
-                    st256(W.idh + 2 * (size_t)slot, make_float4(idf.x, idf.y, __int_as_float((int)g.next), __int_as_float(depth + 1)),
+                    st256(W.ray_out + 2 * (size_t)j, make_float4(h.p[0], h.p[1], h.p[2], stime), make_float4(sd[0], sd[1], sd[2], T[0]));
+                    st256(W.idh_out + 2 * (size_t)j, make_float4(idf.x, idf.y, __int_as_float((int)g.next), __int_as_float(depth + 1)),
                           make_float4(0.f, __int_as_float(-1), T[1], T[2]));
                     // (a surface that both emits and scatters does not exist behind this API; if one ever did, its emission goes
                     // to the pixel here instead of being carried)
@@ -389,7 +423,7 @@ __global__ void __launch_bounds__(256, 4) wf_shade_kernel(DScene S, WavefrontLau
     }
     if (ended) wf_add_pixel(W, pixel, Lr);
     bool dead;
-    wf_refill(W, cam, ended, valid ? slot : 0, dead, early, early_base);
+    wf_refill(W, cam, ended, (int)j, dead, early, early_base);      // the successor of an ended path starts in out[j]
 }
 
 __global__ void wf_finalize_kernel(const unsigned long long *__restrict__ fixed, float *__restrict__ accum, size_t n, double inv_scale) {
@@ -403,65 +437,109 @@ __global__ void wf_finalize_kernel(const unsigned long long *__restrict__ fixed,
 cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaunch &W, float *d_accum, float *d_accum_sq, unsigned long long *h_pinned,
                           cudaStream_t stream, uint32_t *launches_out, WavefrontProfile *prof) {
     // Lane refill pays when traversals are long (a million spheres: ~55 node visits per ray); on a scene of a few dozen
-    // nodes a ray takes ~3 steps and the refill's load latency would dominate, so a warp then simply runs batches of 32
-    // (measured on the 101-object scene: 1.43 -> 1.95 Gpaths/s).
+    // nodes a ray takes ~3 steps and the refill's load latency would dominate, so a warp then simply runs batches of 32.
     static const int refill_env = [] { const char *e = getenv("RTOW_WF_REFILL"); return e ? atoi(e) : -1; }();
     const int refill = refill_env >= 0 ? refill_env : (S.fast_n_nodes >= 4096 ? 28 : 1);
     static const int leaf_min = [] { const char *e = getenv("RTOW_TRACE_LEAFMIN"); return e ? atoi(e) : 8; }();
-    int dev = 0, sms = 148, per_sm = 4;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     // BVH scenes: 5 blocks x 96 registers (the traversal state stays in registers); list scenes run the reference list
     // walk, which is call-heavy rather than state-heavy: 8 blocks x 64 registers measured 6 % faster (smoke scene)
     static const int minb_env = [] { const char *e = getenv("RTOW_WF_MINB"); return e ? atoi(e) : 0; }();   // tuning knob
     const int minb = minb_env ? minb_env : (S.fast_nodes ? 5 : 8);
-    static const int exact_env = [] { const char *e = getenv("RTOW_WF_EXACT_KERNEL"); return e ? atoi(e) : 1; }();   // 0: A/B against wf_extend_kernel
-    static const int debug_exact_every = [] { const char *e = getenv("RTOW_WF_DEBUG_EXACT_EVERY"); return e ? atoi(e) : 0; }();   // tests: every n-th slot takes the in-kernel fallback to the reference walk
+    static const int debug_exact_every = [] { const char *e = getenv("RTOW_WF_DEBUG_EXACT_EVERY"); return e ? atoi(e) : 0; }();   // tests: every n-th entry takes the in-kernel fallback to the reference walk
     static const int exact_minb = [] { const char *e = getenv("RTOW_WF_EXACT_MINB"); return e ? atoi(e) : 8; }();
-    const bool exact_walk = exact_env && !(W.L.traverse == RTOW_TRAVERSE_FAST && S.fast_nodes != nullptr);
-    if (minb >= 8) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_extend_kernel<8>, 128, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_extend_kernel<5>, 128, 0);
-    const unsigned ext_blocks = (unsigned)std::min<long long>((W.pool + 127) / 128, (long long)sms * std::max(per_sm, 1));
-    const unsigned pool_blocks = (unsigned)(W.pool / 256);
+    const bool fast = W.L.traverse == RTOW_TRAVERSE_FAST && S.fast_nodes != nullptr;
+    int dev = 0, sms = 148, per_sm_bvh = 4, per_sm_exact = 8;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (minb >= 8) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_bvh, wf_extend_kernel<8>, 128, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_bvh, wf_extend_kernel<5>, 128, 0);
+    if (exact_minb >= 8) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_exact, wf_extend_exact_kernel<8>, 128, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_exact, wf_extend_exact_kernel<5>, 128, 0);
     const size_t n_acc = (size_t)W.L.pixel_count * 3;
     uint32_t launches = 0;
+
+    // work-item geometry for wf_item_to_pixel
+    const unsigned long long padded = ((unsigned long long)W.L.pixel_count + 31ull) & ~31ull;
+    W.block_items = padded * WF_SAMPLE_BLOCK;
+    W.full_blocks = (unsigned)W.L.sample_count / WF_SAMPLE_BLOCK;
+    W.full_items = (unsigned long long)W.full_blocks * W.block_items;
+    W.inv_block_items = 1.0 / (double)W.block_items;
 
     cudaMemsetAsync(W.fixed, 0, n_acc * sizeof(unsigned long long), stream);
     if (W.fixed_sq) cudaMemsetAsync(W.fixed_sq, 0, n_acc * sizeof(unsigned long long), stream);
     cudaMemsetAsync(W.control, 0, RTOW_WF_CONTROL_WORDS * sizeof(unsigned long long), stream);
     cudaMemsetAsync(W.counts, 0, 2 * RTOW_WF_MAX_CLASSES * sizeof(unsigned), stream);
-    wf_generate_kernel<<<pool_blocks, 256, 0, stream>>>(W, cam);
+    int cur = 0;                               // generate fills buffer 0; bounce i reads buffer i & 1 and writes the other
+    W.ray_out = W.ray_buf[0]; W.idh_out = W.idh_buf[0];
+    W.ray_in = W.ray_buf[1]; W.idh_in = W.idh_buf[1];
+    wf_generate_kernel<<<(unsigned)(W.pool / 256), 256, 0, stream>>>(W, cam);
     launches++;
-    // Every slot traces one ray per iteration; slots die only when the work items run out, so the loop needs about
-    // total_rays / pool iterations plus a tail of at most max_depth.  The dead-slot counter is read back every few
-    // iterations (the reads lag the launches; extra iterations over a dead pool cost ~10 us each).
+    // Every live entry traces one ray per iteration; entries die only when the work items run out, so the loop needs about
+    // total_rays / pool iterations plus a drain of at most max_depth.  The host launches iterations back to back and looks
+    // at the device's counters (work items handed out, dead entries) only now and then: while work remains, the next look
+    // is scheduled from the measured items-per-iteration rate at 70 % of what is left (a handful of synchronisations per
+    // frame); in the drain it looks every 4 iterations and sizes the grids by the entries still alive -- the stream is dense,
+    // so bounce b + 1 has exactly as many entries as were alive after bounce b - 1, and fewer from then on.
     int parity = 0;
-    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     if (prof) { for (auto &e : ev) cudaEventCreate(&e); *prof = WavefrontProfile(); }
+    long long shade_bound = W.pool, extend_bound = W.pool;
+    long long next_poll = W.total_items <= (unsigned long long)W.pool ? 0 : 7;
+    uint32_t tail_iters = 0, polls = 0, iters = 0;
+    bool exhausted = false;
     for (long long it = 0;; ++it) {
-        const bool sampled = prof && ((it & 7) == 6 || W.total_items <= (unsigned long long)W.pool);   // timed just before a sync point
+        const bool poll = it >= next_poll;
+        const bool sampled = prof && poll;       // timed just before a synchronisation point
+        W.ray_in = W.ray_buf[cur]; W.idh_in = W.idh_buf[cur];
+        W.ray_out = W.ray_buf[cur ^ 1]; W.idh_out = W.idh_buf[cur ^ 1];
         if (sampled) cudaEventRecord(ev[0], stream);
-        if (exact_walk && exact_minb >= 8) wf_extend_exact_kernel<8><<<(unsigned)(W.pool / 128), 128, 0, stream>>>(S, W, parity);
-        else if (exact_walk && exact_minb >= 6) wf_extend_exact_kernel<6><<<(unsigned)(W.pool / 128), 128, 0, stream>>>(S, W, parity);
-        else if (exact_walk) wf_extend_exact_kernel<5><<<(unsigned)(W.pool / 128), 128, 0, stream>>>(S, W, parity);
-        else if (minb >= 8) wf_extend_kernel<8><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, debug_exact_every);
-        else wf_extend_kernel<5><<<ext_blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, debug_exact_every);
-        if (sampled) cudaEventRecord(ev[1], stream);
-        wf_shade_kernel<<<pool_blocks, 256, 0, stream>>>(S, W, cam, parity);
-        if (sampled) cudaEventRecord(ev[2], stream);
-        launches += 2;
-        parity ^= 1;
-        if ((it & 7) == 7 || W.total_items <= (unsigned long long)W.pool) {
-            cudaMemcpyAsync(h_pinned, W.dead_slots, sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream);
-            cudaError_t e = cudaStreamSynchronize(stream);
-            if (e != cudaSuccess) return e;
-            if (prof && (it & 7) == 7 && *h_pinned == 0) {   // the sampled iteration ran on a full pool: count it
-                float a = 0.f, b = 0.f;
-                cudaEventElapsedTime(&a, ev[0], ev[1]); cudaEventElapsedTime(&b, ev[1], ev[2]);
-                prof->extend_ms += a; prof->shade_ms += b; prof->samples++;
-            }
-            if (*h_pinned >= (unsigned long long)W.pool) break;
+        if (fast) {
+            const unsigned blocks = (unsigned)std::max<long long>(1, std::min<long long>((extend_bound + 127) / 128, (long long)sms * std::max(per_sm_bvh, 1)));
+            if (minb >= 8) wf_extend_kernel<8><<<blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, debug_exact_every);
+            else wf_extend_kernel<5><<<blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, debug_exact_every);
+        } else {
+            const unsigned blocks = (unsigned)std::max<long long>(1, (extend_bound + 127) / 128);      // (grid-stride inside: any grid is correct)
+            if (exact_minb >= 8) wf_extend_exact_kernel<8><<<blocks, 128, 0, stream>>>(S, W, parity);
+            else if (exact_minb >= 6) wf_extend_exact_kernel<6><<<blocks, 128, 0, stream>>>(S, W, parity);
+            else wf_extend_exact_kernel<5><<<blocks, 128, 0, stream>>>(S, W, parity);
         }
+        if (sampled) cudaEventRecord(ev[1], stream);
+        wf_shade_kernel<<<(unsigned)std::max<long long>(1, (shade_bound + 255) / 256), 256, 0, stream>>>(S, W, cam, parity);
+        if (sampled) cudaEventRecord(ev[2], stream);
+        launches += 2; iters++;
+        parity ^= 1; cur ^= 1;
+        if (exhausted) tail_iters++;
+        if (!poll) continue;
+        cudaMemcpyAsync(h_pinned, W.control, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream);     // [0] items handed out, [1] dead entries
+        cudaError_t e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) return e;
+        polls++;
+        const unsigned long long handed = std::min(h_pinned[0], W.total_items), dead = h_pinned[1];
+        if (prof && dead == 0) {                 // the sampled iteration ran on a full pool: count it
+            float a = 0.f, b = 0.f;
+            cudaEventElapsedTime(&a, ev[0], ev[1]); cudaEventElapsedTime(&b, ev[1], ev[2]);
+            prof->extend_ms += a; prof->shade_ms += b; prof->samples++;
+        }
+        if (dead >= (unsigned long long)W.pool) break;
+        if (handed < W.total_items) {
+            const double per_iter = (double)handed / (double)(it + 1);
+            const double left = (double)(W.total_items - handed) / std::max(per_iter, 1.0);
+            next_poll = it + std::max<long long>(4, std::min<long long>(256, (long long)(0.7 * left)));
+        } else {
+            if (!exhausted && prof) cudaEventRecord(ev[3], stream);      // the drain starts (within a poll interval of) here
+            exhausted = true;
+            next_poll = it + 4;
+            // alive now = entries the NEXT shade pass processes; the next extend pass still reads the entries of this bounce
+            // (alive before its shade pass retired some): bounded by what was alive at the previous look
+            const long long live = (long long)W.pool - (long long)dead;
+            extend_bound = shade_bound;
+            shade_bound = live;
+        }
+    }
+    if (prof && exhausted) {
+        cudaEventRecord(ev[2], stream);
+        cudaEventSynchronize(ev[2]);
+        cudaEventElapsedTime(&prof->tail_ms, ev[3], ev[2]);
     }
     wf_finalize_kernel<<<(unsigned)((n_acc + 255) / 256), 256, 0, stream>>>(W.fixed, d_accum, n_acc, 1.0 / WF_FIXED_SCALE);
     launches++;
@@ -470,7 +548,11 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
         launches++;
     }
     if (launches_out) *launches_out = launches;
-    if (prof) { prof->iterations = (uint32_t)((launches - 2 - (W.fixed_sq && d_accum_sq ? 1 : 0)) / 2); prof->pool = (uint32_t)W.pool; for (auto &e : ev) cudaEventDestroy(e); }
+    if (prof) {
+        prof->iterations = iters; prof->pool = (uint32_t)W.pool;
+        prof->tail_iterations = tail_iters; prof->polls = polls;
+        for (auto &e : ev) cudaEventDestroy(e);
+    }
     return cudaGetLastError();
 }
 
