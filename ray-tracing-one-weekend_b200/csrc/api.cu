@@ -507,6 +507,7 @@ int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out)
             }
             if ((rc = upload(s, fb.spheres.data(), fb.spheres.size(), &D.fast_spheres))) return rc;
             if ((rc = upload(s, fb.guards.data(), fb.guards.size(), &D.fast_guards))) return rc;
+            if ((rc = upload(s, fb.moving.data(), fb.moving.size(), &D.fast_moving))) return rc;
             s->has_fast = true;
         }
     }

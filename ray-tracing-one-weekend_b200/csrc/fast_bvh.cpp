@@ -221,15 +221,26 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
         const rtow_object &ob = d->objects[o];
         const rtow_prim &p0 = d->prims[ob.prim_begin];
         bool simple = ob.prim_count == 1 && p0.type == RTOW_PRIM_SPHERE && p0.xform_count == 0;
+        bool moving = ob.prim_count == 1 && p0.type == RTOW_PRIM_MOVING_SPHERE && p0.xform_count == 0;
         bool has_medium = false;
         for (int p = ob.prim_begin; p < ob.prim_begin + ob.prim_count; ++p) has_medium |= d->prims[p].type == RTOW_PRIM_MEDIUM;
         int32_t code = o;
         if (simple) code |= FAST_LEAF_SPHERE;
+        if (moving) code |= FAST_LEAF_MOVING;
         if (twice[o] && has_medium) code |= FAST_LEAF_TWICE;
         leaf_ref[o] = ~code;
         out.guards[(size_t)o * 2 + 0] = make_float4(g.bmin[0], g.bmin[1], g.bmin[2], 0.f);
         out.guards[(size_t)o * 2 + 1] = make_float4(g.bmax[0], g.bmax[1], g.bmax[2], 0.f);
         if (simple) out.spheres[o] = make_float4(p0.f[0], p0.f[1], p0.f[2], p0.f[3]);
+        if (moving) {
+            // rtow_prim: f[0..2] centre0, f[3..5] centre1, f[6] time0, f[7] time1, f[8] radius.  centre(time) =
+            // c0 + ((time - t0) / (t1 - t0)) * (c1 - c0) (sphere.h:129-131): the two differences do not depend on the ray
+            if (out.moving.empty()) out.moving.assign((size_t)n * 2, make_float4(0, 0, 0, 0));
+            volatile float dx = p0.f[3] - p0.f[0], dy = p0.f[4] - p0.f[1], dz = p0.f[5] - p0.f[2], dt = p0.f[7] - p0.f[6];   // single float subtractions, as the device does them
+            out.spheres[o] = make_float4(p0.f[0], p0.f[1], p0.f[2], p0.f[8]);
+            out.moving[(size_t)o * 2 + 0] = make_float4(dx, dy, dz, p0.f[6]);
+            out.moving[(size_t)o * 2 + 1] = make_float4(dt, 0.f, 0.f, 0.f);
+        }
     }
 
     Builder B(boxes);

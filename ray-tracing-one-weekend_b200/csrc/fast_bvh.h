@@ -31,7 +31,10 @@ namespace rtow {
 //       inverted byte interval (255..0) and refers to the never-hit sphere spheres[n_objects] (NaN radius), so the
 //       kernel needs no test for it
 // Per object (leaf), indexed by object id:
-//   spheres[obj]        {cx,cy,cz,r} of a bare Sphere leaf (FAST_LEAF_SPHERE), else zeros; one extra never-hit entry
+//   spheres[obj]        {cx,cy,cz,r} of a bare Sphere leaf (FAST_LEAF_SPHERE) or {c0, r} of a bare MovingSphere leaf
+//                       (FAST_LEAF_MOVING), else zeros; one extra never-hit entry
+//   moving[2*obj..+1]   bare MovingSphere leaves only (empty when the scene has none): {c1 - c0, time0} {time1 - time0, -, -, -};
+//                       the two differences are the float subtractions sphere.h:129-131 performs per call, done once here
 //   guards[2*obj..+1]   {bmin.xyz, -} {bmax.xyz, -}: box of the reference BvhNode that owns the leaf
 enum { FAST_NODE_F4 = 4 };
 static const int32_t FAST_EMPTY = 0x7fffffff;   // builder-internal marker of an unused slot
@@ -39,13 +42,15 @@ static const uint32_t FAST_NODE_BIAS_WORD = 0x47000000u;
 enum {
     FAST_LEAF_SPHERE = 1 << 30,   // the object is one untransformed Sphere: test spheres[obj] directly
     FAST_LEAF_TWICE = 1 << 29,    // n==1 node holding a medium: the reference evaluates it twice (bvhNode.h:38-40,70-71)
-    FAST_LEAF_ID_MASK = (1 << 29) - 1
+    FAST_LEAF_MOVING = 1 << 28,   // the object is one untransformed MovingSphere: spheres[obj] + moving[2*obj..]
+    FAST_LEAF_ID_MASK = (1 << 28) - 1
 };
 
 struct FastBvh {
     std::vector<float4> nodes;    // FAST_NODE_F4 per node
     std::vector<float4> spheres;  // one per object
     std::vector<float4> guards;   // two per object
+    std::vector<float4> moving;   // two per object, or empty
     int32_t root = 0;
     float center[3] = {0, 0, 0};
     float radius = 0;             // bounds every primitive box and centre, from `center`

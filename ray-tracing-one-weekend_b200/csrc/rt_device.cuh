@@ -51,6 +51,7 @@ struct DScene {
     const float4 *fast_spheres;   // per object: {c, r} of a bare Sphere leaf (fast_bvh.h)
     const int *prim_class;        // shading class (wavefront queues) per primitive
     const float4 *fast_guards;    // per object: 2 x float4, box of the reference node that owns the leaf
+    const float4 *fast_moving;    // per object: 2 x float4 {c1 - c0, time0} {time1 - time0} of a bare MovingSphere leaf (null: none in the scene)
     float scene_center[3];
     float scene_radius;           // bounds all primitive boxes (for the culling slack)
     float fast_time_lo, fast_time_hi;   // ray times for which the moving-sphere cull boxes hold

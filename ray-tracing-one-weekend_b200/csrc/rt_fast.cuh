@@ -281,16 +281,24 @@ __device__ __forceinline__ void fast_leaf(const DScene &S, FastTrav &T, const KE
     const int code = ~T.cur;
     const int obj = code & FAST_LEAF_ID_MASK;
     float t = 0.f; int pid = -1; bool h;
-    if (code & FAST_LEAF_SPHERE) {
+    if (code & (FAST_LEAF_SPHERE | FAST_LEAF_MOVING)) {
         if (COUNT) prim_tests++;
-        const float4 sph = __ldg(S.fast_spheres + obj);
+        float4 sph = __ldg(S.fast_spheres + obj);
+        if (code & FAST_LEAF_MOVING) {
+            // sphere.h:129-131: centre(time) = c0 + ((time - t0) / (t1 - t0)) * (c1 - c0); the builder did the two
+            // ray-independent subtractions (fast_bvh.cpp), the rest is the reference's arithmetic in its order
+            float4 m0, m1;
+            ldg256(S.fast_moving + 2 * (size_t)obj, m0, m1);
+            const float k = (T.r.time - m0.w) / m1.x;
+            sph.x = sph.x + k * m0.x; sph.y = sph.y + k * m0.y; sph.z = sph.z + k * m0.z;
+        }
         h = sphere_t(sph.x, sph.y, sph.z, sph.w, T.r, T.tmin, T.tmax, t);
     } else {
         const RngKey key = key_of();
         Rng g;
         rng_init(g, key.seed, key.pixel, key.sample);
         g.bounce = key.bounce;
-        // a leaf that is not a bare sphere: a run of primitives (Box, MovingSphere, wrapped objects, media), out of line
+        // a leaf that is not a bare sphere: a run of primitives (Box, wrapped objects, media), out of line
         const int4 o = __ldg(&S.objects[obj]);
         h = object_hit<COUNT>(S, T.r, T.tmin, T.tmax, &g, o.x, o.y, 0, (code & FAST_LEAF_TWICE) ? 2 : 1, t, pid, prim_tests);
     }

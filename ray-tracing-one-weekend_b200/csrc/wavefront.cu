@@ -331,9 +331,7 @@ __global__ void __launch_bounds__(256, 4) wf_shade_kernel(DScene S, WavefrontLau
         }
         if (lane < RTOW_WF_MAX_CLASSES) s_end[lane] = v;
     }
-    perlin_stage(S, &perlin);
     __syncthreads();
-
     const unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j == 0) {
         // the extend launch of this bounce is complete: reset what the next one uses
@@ -341,6 +339,9 @@ __global__ void __launch_bounds__(256, 4) wf_shade_kernel(DScene S, WavefrontLau
         unsigned *other = W.counts + (parity ^ 1) * RTOW_WF_MAX_CLASSES;
         for (int c = 0; c < RTOW_WF_MAX_CLASSES; ++c) other[c] = 0u;
     }
+    if (blockIdx.x * blockDim.x >= s_end[RTOW_WF_MAX_CLASSES - 1]) return;      // nothing queued for this block (the drain runs oversized grids)
+    perlin_stage(S, &perlin);
+    __syncthreads();
     // queues are consumed class after class: thread j -> (class, index)
     int cls = 0;
 #pragma unroll
@@ -478,8 +479,8 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
     // total_rays / pool iterations plus a drain of at most max_depth.  The host launches iterations back to back and looks
     // at the device's counters (work items handed out, dead entries) only now and then: while work remains, the next look
     // is scheduled from the measured items-per-iteration rate at 70 % of what is left (a handful of synchronisations per
-    // frame); in the drain it looks every 4 iterations and sizes the grids by the entries still alive -- the stream is dense,
-    // so bounce b + 1 has exactly as many entries as were alive after bounce b - 1, and fewer from then on.
+    // frame); once the work is exhausted it sizes the grids by the entries still alive (the stream is dense: bounce b + 1 has
+    // exactly as many entries as were alive after bounce b - 1, and fewer from then on) and launches the whole drain blind.
     int parity = 0;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     if (prof) { for (auto &e : ev) cudaEventCreate(&e); *prof = WavefrontProfile(); }
@@ -527,8 +528,11 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
             next_poll = it + std::max<long long>(4, std::min<long long>(256, (long long)(0.7 * left)));
         } else {
             if (!exhausted && prof) cudaEventRecord(ev[3], stream);      // the drain starts (within a poll interval of) here
+            // Every path alive now ends within max_depth + 1 more bounces: those iterations are launched back to back with no
+            // look in between (a look empties the launch queue: ~50 us of bubbles each against ~10 us iterations); blocks
+            // beyond the shrinking stream exit at once.  Should anything be left after that, looks resume every 4 iterations.
+            next_poll = it + (exhausted ? 4 : (long long)W.L.max_depth + 2);
             exhausted = true;
-            next_poll = it + 4;
             // alive now = entries the NEXT shade pass processes; the next extend pass still reads the entries of this bounce
             // (alive before its shade pass retired some): bounded by what was alive at the previous look
             const long long live = (long long)W.pool - (long long)dead;
