@@ -408,6 +408,35 @@ int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out)
             p.xform_count |= key << 8;
         }
         if ((rc = upload(s, (const int4 *)dp.data(), (size_t)desc->n_prims * 5, &D.prims))) return rc;
+        // Compiled form of a list scene (rt_device.cuh list_hit): every wrapper chain must read [Translate] [RotateY] once the
+        // FlipNormals are dropped, no MovingSphere, at most RTOW_LIST_MAX primitives; anything else keeps the generic walk.
+        if (desc->top_kind == RTOW_TOP_LIST && desc->n_prims > 0 && desc->n_prims <= RTOW_LIST_MAX) {
+            std::vector<float4> prog((size_t)desc->n_prims * 4, make_float4(0, 0, 0, 0));
+            bool ok = true;
+            for (int i = 0; i < desc->n_prims && ok; ++i) {
+                const rtow_prim &p = desc->prims[i];
+                int form = 0;
+                float T[3] = {0, 0, 0}, sn = 0, cs = 0;
+                for (int k = p.xform_begin; k < p.xform_begin + p.xform_count && ok; ++k) {
+                    const rtow_xform &x = desc->xforms[k];
+                    if (x.type == RTOW_XF_FLIP) continue;
+                    if (x.type == RTOW_XF_TRANSLATE && form == 0) { form = RTOW_LIST_FORM_T; T[0] = x.f[0]; T[1] = x.f[1]; T[2] = x.f[2]; }
+                    else if (x.type == RTOW_XF_ROTATE_Y && !(form & RTOW_LIST_FORM_R)) { form |= RTOW_LIST_FORM_R; sn = x.f[0]; cs = x.f[1]; }
+                    else ok = false;
+                }
+                if (p.type == RTOW_PRIM_MOVING_SPHERE) ok = false;
+                auto fi = [](int32_t v) { float f; std::memcpy(&f, &v, 4); return f; };
+                const int key = (int)((uint32_t)dp[i].xform_count >> 8);
+                prog[4 * (size_t)i + 0] = make_float4(fi(p.type | (form << 8)), fi(key), fi(p.child_begin), fi(p.child_count));
+                prog[4 * (size_t)i + 1] = make_float4(T[0], T[1], T[2], p.type == RTOW_PRIM_MEDIUM ? p.f[0] : 0.f);
+                prog[4 * (size_t)i + 2] = make_float4(sn, cs, p.f[0], p.f[1]);
+                prog[4 * (size_t)i + 3] = make_float4(p.f[2], p.f[3], p.f[4], 0.f);
+            }
+            if (ok) {
+                if ((rc = upload(s, prog.data(), prog.size(), &D.list_prog))) return rc;
+                D.list_n = desc->n_prims;
+            }
+        }
     }
     if ((rc = upload(s, (const float4 *)desc->xforms, (size_t)desc->n_xforms, &D.xforms))) return rc;
 

@@ -51,6 +51,10 @@ struct DScene {
     const float4 *fast_spheres;   // per object: {c, r} of a bare Sphere leaf (fast_bvh.h)
     const int *prim_class;        // shading class (wavefront queues) per primitive
     const float4 *fast_guards;    // per object: 2 x float4, box of the reference node that owns the leaf
+    // compiled form of a list scene (wf_extend_list_kernel; null when the scene does not qualify, see api.cu compile_list):
+    // 4 x float4 per primitive {kind | form << 8, ray key, child_begin, child_count} {T.xyz, density} {sin, cos, f0, f1} {f2, f3, f4, -}
+    const float4 *list_prog;
+    int32_t list_n;               // records = all primitives (top-level run first, media boundaries after)
     const float4 *fast_moving;    // per object: 2 x float4 {c1 - c0, time0} {time1 - time0} of a bare MovingSphere leaf (null: none in the scene)
     float scene_center[3];
     float scene_radius;           // bounds all primitive boxes (for the culling slack)
@@ -369,6 +373,96 @@ __device__ __noinline__ bool object_hit(const DScene &S, const Ray r, float tmin
         if (run_hit<COUNT>(S, begin, count, r, tmin, tmax, g, visit0 + v, t2, pid2, prim_tests) && !(h && t < t2)) { h = true; t = t2; pid = pid2; }
     }
     return h;
+}
+
+// ---- HitableList::hit over the compiled form of a list scene -----------------------------------------------------
+// The same walk as run_hit / medium_t / simple_prim_t above -- element i sees tmax = closest so far (hitableList.h:20-38),
+// wrappers applied to the ray outermost first (hitable.h:53-62,125-154), one transformed ray reused across neighbours with
+// equal chains -- but read from fixed-form records in shared memory instead of interpreting rtow_prim + rtow_xform lists:
+// every wrapper chain of a qualifying scene is [Translate] [RotateY] (FlipNormals does not move the ray), so a record
+// carries the offset and the rotation inline.  Arithmetic and its order are unchanged (same t, bit for bit).
+#define RTOW_LIST_MAX 128
+#define RTOW_LIST_FORM_T 1
+#define RTOW_LIST_FORM_R 2
+__device__ __forceinline__ void list_xform(const Ray &r_in, int form, const float4 &q1, const float4 &q2, Ray &r) {
+    r = r_in;
+    if (form & RTOW_LIST_FORM_T) { r.ox = r.ox - q1.x; r.oy = r.oy - q1.y; r.oz = r.oz - q1.z; }          // hitable.h:53-55
+    if (form & RTOW_LIST_FORM_R) {                                                                         // hitable.h:125-135
+        const float s = q2.x, c = q2.y;
+        const float ox = c * r.ox - s * r.oz, oz = s * r.ox + c * r.oz;
+        const float dx = c * r.dx - s * r.dz, dz = s * r.dx + c * r.dz;
+        r.ox = ox; r.oz = oz; r.dx = dx; r.dz = dz;
+    }
+}
+// one non-medium record; `kind` is uniform across the warp (all lanes walk the same list in step)
+__device__ __forceinline__ bool list_prim_t(const float4 *rec, int kind, const Ray &r, float tmin, float tmax, float &t_out) {
+    const float4 q2 = rec[2], q3 = rec[3];
+    if (kind == RTOW_PRIM_SPHERE) return sphere_t(q2.z, q2.w, q3.x, q3.y, r, tmin, tmax, t_out);
+    if (kind == RTOW_PRIM_RECT_XY) return rect_t(q2.z, q2.w, q3.x, q3.y, q3.z, r.oz, r.dz, r.ox, r.dx, r.oy, r.dy, tmin, tmax, t_out);
+    if (kind == RTOW_PRIM_RECT_XZ) return rect_t(q2.z, q2.w, q3.x, q3.y, q3.z, r.oy, r.dy, r.ox, r.dx, r.oz, r.dz, tmin, tmax, t_out);
+    return rect_t(q2.z, q2.w, q3.x, q3.y, q3.z, r.ox, r.dx, r.oy, r.dy, r.oz, r.dz, tmin, tmax, t_out);
+}
+// constantMedium.h:26-74 (medium_t above) on records
+static __device__ __noinline__ bool list_medium_t(const float4 *prog, int pid, const Ray r_in, float tmin, float tmax, const Rng *g, float &t_out) {
+    const float4 *rec = prog + 4 * pid;
+    const float4 q0 = rec[0], q1 = rec[1];
+    Ray r;
+    list_xform(r_in, (__float_as_int(q0.x) >> 8) & 3, q1, rec[2], r);
+    const float density = q1.w;
+    const int cb = __float_as_int(q0.z), cn = __float_as_int(q0.w);
+    float t1 = 0.f, t2 = 0.f;
+    int key = 0;
+    Ray rr = r;
+    float from = -FLT_MAX;
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+        bool any = false;
+        float closest = FLT_MAX, t = 0.f;
+#pragma unroll 1
+        for (int i = cb; i < cb + cn; ++i) {
+            const float4 *c = prog + 4 * i;
+            const float4 c0 = c[0];
+            const int ck = __float_as_int(c0.y);
+            if (ck != key || ck == RTOW_RAY_KEY_NONE) { list_xform(r, (__float_as_int(c0.x) >> 8) & 3, c[1], c[2], rr); key = ck; }
+            float tt;
+            if (list_prim_t(c, __float_as_int(c0.x) & 0xff, rr, from, closest, tt)) { any = true; closest = tt; t = tt; }
+        }
+        if (!any) return false;
+        if (pass == 0) { t1 = t; from = (float)((double)t1 + 0.0001); } else t2 = t;
+    }
+    if (t1 < tmin) t1 = tmin;
+    if (t2 > tmax) t2 = tmax;
+    if (t1 >= t2) return false;
+    if (t1 < 0) t1 = 0;
+    float dlen = len3(r.dx, r.dy, r.dz);
+    float inside = (t2 - t1) * dlen;
+    float U = g ? rng_medium(*g, pid, 0) : 0.5f;
+    float hitDistance = (float)(-(double)(1 / density) * log((double)U));
+    if (hitDistance < inside) { t_out = t1 + hitDistance / dlen; return true; }
+    return false;
+}
+__device__ __forceinline__ bool list_hit(const float4 *prog, int n_top, const Ray &r, float tmin, float tmax, const Rng *g, float &t_out, int &prim_out) {
+    bool any = false;
+    float closest = tmax;
+    int key = 0;
+    Ray rr = r;
+#pragma unroll 1
+    for (int i = 0; i < n_top; ++i) {
+        const float4 *rec = prog + 4 * i;
+        const float4 q0 = rec[0];
+        const int kind = __float_as_int(q0.x) & 0xff;
+        float t;
+        bool h;
+        if (kind == RTOW_PRIM_MEDIUM) {
+            h = list_medium_t(prog, i, r, tmin, closest, g, t);
+        } else {
+            const int k = __float_as_int(q0.y);
+            if (k != key || k == RTOW_RAY_KEY_NONE) { list_xform(r, (__float_as_int(q0.x) >> 8) & 3, rec[1], rec[2], rr); key = k; }
+            h = list_prim_t(rec, kind, rr, tmin, closest, t);
+        }
+        if (h) { any = true; closest = t; t_out = t; prim_out = i; }
+    }
+    return any;
 }
 
 // ---- closest hit, EXACT: the reference tree as is -- box test, then BOTH children with the

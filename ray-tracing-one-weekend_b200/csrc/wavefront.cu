@@ -302,6 +302,47 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_exact_kernel(DScene S, Wa
     if (lane == 0 && rays) atomicAdd(&W.stats[0], (unsigned long long)rays);
 }
 
+// ---- extend, list scenes in compiled form -------------------------------------------------------------------------
+// HitableList worlds (the Cornell scenes): every ray walks the whole list in order (hitableList.h:20-38) -- nothing to cull,
+// all lanes of a warp on the same element.  The generic walk above interprets rtow_prim / rtow_xform records from global
+// memory (ncu, round 2: ~70 executed instructions per primitive test, half of them loads, type dispatch and chain loops);
+// this one reads the scene's fixed-form records (rt_device.cuh list_hit) from shared memory.  Same arithmetic, same hits.
+__global__ void __launch_bounds__(128, 8) wf_extend_list_kernel(DScene S, WavefrontLaunch W, int parity) {
+    __shared__ float4 s_prog[4 * RTOW_LIST_MAX];
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < 4 * S.list_n; i += blockDim.x) s_prog[i] = __ldg(S.list_prog + i);
+    __syncthreads();
+    unsigned *counts = W.counts + parity * RTOW_WF_MAX_CLASSES;
+    const unsigned n = wf_entries(W, parity);
+    unsigned rays = 0;
+    for (unsigned tile = blockIdx.x; (unsigned long long)tile * 128u < n; tile += gridDim.x) {
+        const size_t slot = (size_t)tile * 128u + threadIdx.x;
+        int cls = -1;
+        if (slot < n) {
+            float4 a, b;
+            ld256(W.ray_in + 2 * slot, a, b);
+            if (__float_as_int(b.w) != WF_DEAD_BITS) {
+                const int4 id = W.idh_in[2 * slot];
+                Ray r;
+                r.ox = a.x; r.oy = a.y; r.oz = a.z; r.time = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z;
+                root_ray(S, r);
+                Rng g;
+                rng_init(g, W.L.seed, (uint32_t)id.x, (uint32_t)id.y);
+                g.bounce = (uint32_t)id.w;
+                float t = 0.f; int pid = -1;
+                if (!list_hit(s_prog, S.n_prims_top, r, 0.001f, FLT_MAX, &g, t, pid)) { t = 0.f; pid = -1; }
+                *reinterpret_cast<float2 *>(W.idh_in + 2 * slot + 1) = make_float2(t, __int_as_float(pid));
+                cls = pid >= 0 ? __ldg(&S.prim_class[pid]) : 0;
+                rays++;
+            }
+        }
+        wf_enqueue(W, counts, cls, (int)slot);
+    }
+    for (int off = 16; off; off >>= 1) rays += __shfl_down_sync(full, rays, off);
+    if (lane == 0 && rays) atomicAdd(&W.stats[0], (unsigned long long)rays);
+}
+
 // ---- shade -------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void wf_add_pixel(const WavefrontLaunch &W, int pixel, const float L[3]) {
 #pragma unroll
@@ -449,6 +490,8 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
     static const int debug_exact_every = [] { const char *e = getenv("RTOW_WF_DEBUG_EXACT_EVERY"); return e ? atoi(e) : 0; }();   // tests: every n-th entry takes the in-kernel fallback to the reference walk
     static const int exact_minb = [] { const char *e = getenv("RTOW_WF_EXACT_MINB"); return e ? atoi(e) : 8; }();
     const bool fast = W.L.traverse == RTOW_TRAVERSE_FAST && S.fast_nodes != nullptr;
+    static const int list_env = [] { const char *e = getenv("RTOW_WF_LIST_KERNEL"); return e ? atoi(e) : 1; }();       // 0: the generic walk (A/B, tests)
+    const bool use_list = !fast && list_env && S.top_kind == RTOW_TOP_LIST && S.list_prog != nullptr;
     int dev = 0, sms = 148, per_sm_bvh = 4, per_sm_exact = 8;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -498,6 +541,9 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
             const unsigned blocks = (unsigned)std::max<long long>(1, std::min<long long>((extend_bound + 127) / 128, (long long)sms * std::max(per_sm_bvh, 1)));
             if (minb >= 8) wf_extend_kernel<8><<<blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, debug_exact_every);
             else wf_extend_kernel<5><<<blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, debug_exact_every);
+        } else if (use_list) {
+            const unsigned blocks = (unsigned)std::max<long long>(1, std::min<long long>((extend_bound + 127) / 128, (long long)sms * 8 * 4));
+            wf_extend_list_kernel<<<blocks, 128, 0, stream>>>(S, W, parity);
         } else {
             const unsigned blocks = (unsigned)std::max<long long>(1, (extend_bound + 127) / 128);      // (grid-stride inside: any grid is correct)
             if (exact_minb >= 8) wf_extend_exact_kernel<8><<<blocks, 128, 0, stream>>>(S, W, parity);
