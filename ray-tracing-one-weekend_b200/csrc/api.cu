@@ -171,6 +171,13 @@ void build_entries(const rtow_scene_desc *d, const std::vector<int4> &objs, std:
     }
 }
 
+bool texture_uses_perlin(const rtow_scene_desc *d, int tex) {
+    const rtow_texture &t = d->textures[tex];
+    if (t.type == RTOW_TEX_NOISE) return true;
+    if (t.type == RTOW_TEX_CHECKER) return texture_uses_perlin(d, t.a) || texture_uses_perlin(d, t.b);
+    return false;
+}
+
 bool texture_needs_uv(const rtow_scene_desc *d, int tex) {
     const rtow_texture &t = d->textures[tex];
     if (t.type == RTOW_TEX_IMAGE) return true;
@@ -463,6 +470,7 @@ int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out)
         int key = m.type * 8 + (textured ? desc->textures[m.tex_id].type : 7);
         if (class_of_key[key] < 0) class_of_key[key] = n_classes < RTOW_WF_MAX_CLASSES ? n_classes++ : RTOW_WF_MAX_CLASSES - 1;
         mats[2 * i + 1] = make_int4(f[2], f[3], textured && texture_needs_uv(desc, m.tex_id) ? 1 : 0, class_of_key[key]);
+        if (textured && texture_uses_perlin(desc, m.tex_id)) D.perlin_class_mask |= 1u << class_of_key[key];
     }
     if ((rc = upload(s, mats.data(), mats.size(), &D.materials))) return rc;
     {   // shading class per primitive: one load where prims -> materials were two dependent ones at the end of every extend batch

@@ -55,6 +55,7 @@ struct DScene {
     // 4 x float4 per primitive {kind | form << 8, ray key, child_begin, child_count} {T.xyz, density} {sin, cos, f0, f1} {f2, f3, f4, -}
     const float4 *list_prog;
     int32_t list_n;               // records = all primitives (top-level run first, media boundaries after)
+    uint32_t perlin_class_mask;   // bit c: shading class c may evaluate Perlin noise (wf_shade_kernel stages the tables only then)
     const float4 *fast_moving;    // per object: 2 x float4 {c1 - c0, time0} {time1 - time0} of a bare MovingSphere leaf (null: none in the scene)
     float scene_center[3];
     float scene_radius;           // bounds all primitive boxes (for the culling slack)

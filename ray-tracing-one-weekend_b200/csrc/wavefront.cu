@@ -171,7 +171,7 @@ __device__ __forceinline__ void wf_enqueue(const WavefrontLaunch &W, unsigned *c
 
 // ---- extend ------------------------------------------------------------------------------------------------
 template <int MINB>
-__global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, WavefrontLaunch W, int parity, int refill_below, int leaf_min, int debug_exact_every) {
+__global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, WavefrontLaunch W, int parity, int refill_below, int leaf_min, int debug_exact_every, int static_claim) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     __shared__ uint2 s_stack[RTOW_WF_STACK_SMEM * 128];
@@ -191,6 +191,7 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
     unsigned *counts = W.counts + parity * RTOW_WF_MAX_CLASSES;
     const bool use_fast = W.L.traverse == RTOW_TRAVERSE_FAST && S.fast_nodes != nullptr;
     const unsigned long long n = wf_entries(W, parity);
+    unsigned next_batch = blockIdx.x * 4u + (threadIdx.x >> 5);
 
     for (;;) {
         // 1. finished lanes: write {t, prim} and queue the entry under its shading class
@@ -214,8 +215,15 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_kernel(DScene S, Wavefron
         if (more) {
             const unsigned need = __ballot_sync(full, !has_ray);
             unsigned long long base = 0;
-            if (lane == 0) base = atomicAdd(W.extend_head, (unsigned long long)__popc(need));
-            base = __shfl_sync(full, base, 0);
+            if (static_claim) {
+                // whole batches of 32 (refill_below == 1: a warp only comes here with all lanes idle), dealt round-robin to
+                // the resident warps: no counter to ask
+                base = (unsigned long long)next_batch * 32ull;
+                next_batch += gridDim.x * 4u;
+            } else {
+                if (lane == 0) base = atomicAdd(W.extend_head, (unsigned long long)__popc(need));
+                base = __shfl_sync(full, base, 0);
+            }
             if (base + __popc(need) >= n) more = false;
             if (!has_ray) {
                 const unsigned long long mine = base + __popc(need & ((1u << lane) - 1u));
@@ -359,50 +367,58 @@ __device__ __forceinline__ void wf_add_pixel(const WavefrontLaunch &W, int pixel
 
 __global__ void __launch_bounds__(256, 4) wf_shade_kernel(DScene S, WavefrontLaunch W, rtow_camera cam, int parity) {
     __shared__ PerlinSmem perlin;
-    __shared__ unsigned s_end[RTOW_WF_MAX_CLASSES];     // running totals of the class queue lengths
+    __shared__ unsigned long long s_early_base;
     static_assert(RTOW_WF_MAX_CLASSES <= 32, "one warp scans the class counts");
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const unsigned *counts = W.counts + parity * RTOW_WF_MAX_CLASSES;
-    if (threadIdx.x < 32) {       // one load per class and a warp scan, instead of a chain of dependent loads in every thread
-        unsigned v = lane < RTOW_WF_MAX_CLASSES ? counts[lane] : 0u;
-        for (int o = 1; o < RTOW_WF_MAX_CLASSES; o <<= 1) {
-            const unsigned u = __shfl_up_sync(full, v, o);
-            if (lane >= o) v += u;
-        }
-        if (lane < RTOW_WF_MAX_CLASSES) s_end[lane] = v;
+    // Every warp scans the class counts for itself (one load per class + shuffles; lane c keeps the running total of
+    // classes 0..c): no shared memory and no block barrier between the kernel's start and the queue -> state chain of loads.
+    unsigned endc = lane < RTOW_WF_MAX_CLASSES ? counts[lane] : 0u;
+    for (int o = 1; o < RTOW_WF_MAX_CLASSES; o <<= 1) {
+        const unsigned u = __shfl_up_sync(full, endc, o);
+        if (lane >= o) endc += u;
     }
-    __syncthreads();
-    const unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned total = __shfl_sync(full, endc, RTOW_WF_MAX_CLASSES - 1), end0 = __shfl_sync(full, endc, 0);
+    const unsigned blk0 = blockIdx.x * blockDim.x;
+    const unsigned j = blk0 + threadIdx.x;
     if (j == 0) {
         // the extend launch of this bounce is complete: reset what the next one uses
         *W.extend_head = 0ull;
         unsigned *other = W.counts + (parity ^ 1) * RTOW_WF_MAX_CLASSES;
         for (int c = 0; c < RTOW_WF_MAX_CLASSES; ++c) other[c] = 0u;
     }
-    if (blockIdx.x * blockDim.x >= s_end[RTOW_WF_MAX_CLASSES - 1]) return;      // nothing queued for this block (the drain runs oversized grids)
-    perlin_stage(S, &perlin);
-    __syncthreads();
+    if (blk0 >= total) return;      // nothing queued for this block (the drain runs oversized grids); block-uniform
+    // Class 0 holds the rays that hit nothing: those paths end for certain, and they are the first end0 entries.  ONE atomic
+    // per block claims the next work items for all of them now (every warp of every block used to ask the same counter:
+    // ~50 K same-address atomics per launch), and its round trip runs under the state loads.
+    const unsigned n0 = end0 > blk0 ? min(end0 - blk0, blockDim.x) : 0u;
+    if (threadIdx.x == 0 && n0) s_early_base = atomicAdd(W.next_item, (unsigned long long)n0);
+    // does this block shade a class that evaluates Perlin noise?  (block-uniform: every warp holds the same totals)
+    const unsigned startc = __shfl_up_sync(full, endc, 1);
+    const bool noisy = lane < RTOW_WF_MAX_CLASSES && ((S.perlin_class_mask >> lane) & 1u) && (lane ? startc : 0u) < blk0 + blockDim.x && endc > blk0;
+    const bool need_perlin = S.has_perlin && __any_sync(full, noisy);
     // queues are consumed class after class: thread j -> (class, index)
     int cls = 0;
 #pragma unroll
-    for (int c = 0; c < RTOW_WF_MAX_CLASSES - 1; ++c) cls += j >= s_end[c] ? 1 : 0;
-    const bool valid = j < s_end[RTOW_WF_MAX_CLASSES - 1];
-    // Class 0 holds the rays that hit nothing: those paths end for certain, so their lanes claim the next work items now
-    // and the atomic's round trip runs under the state loads instead of after the shading (it was 18 % of this kernel's
-    // stall samples).
-    const unsigned early = __ballot_sync(full, valid && cls == 0);
-    unsigned long long early_base = 0ull;
-    if (early && lane == 0) early_base = atomicAdd(W.next_item, (unsigned long long)__popc(early));
+    for (int c = 0; c < RTOW_WF_MAX_CLASSES - 1; ++c) cls += j >= __shfl_sync(full, endc, c) ? 1 : 0;
+    const bool valid = j < total;
+    const unsigned cls_start = __shfl_sync(full, endc, cls > 0 ? cls - 1 : 0);
     int slot = -1;
-    if (valid) slot = W.queue[(size_t)cls * W.pool + (j - (cls ? s_end[cls - 1] : 0u))];
+    if (valid) slot = W.queue[(size_t)cls * W.pool + (j - (cls ? cls_start : 0u))];
+    float4 a, b, idf, hf;
+    if (valid) {
+        ld256(W.ray_in + 2 * (size_t)slot, a, b);
+        ld256(W.idh_in + 2 * (size_t)slot, idf, hf);
+    }
+    if (need_perlin) perlin_stage(S, &perlin);      // with the state loads in flight
+    if (need_perlin || n0) __syncthreads();
+    const unsigned early = __ballot_sync(full, valid && cls == 0);
+    const unsigned long long early_base = early ? s_early_base + (threadIdx.x & ~31u) : 0ull;      // class-0 threads are the block's first n0
     bool ended = false;
     int pixel = 0;
     float Lr[3] = {0.f, 0.f, 0.f};
     if (valid) {
-        float4 a, b, idf, hf;
-        ld256(W.ray_in + 2 * (size_t)slot, a, b);
-        ld256(W.idh_in + 2 * (size_t)slot, idf, hf);
         const int4 id = make_int4(__float_as_int(idf.x), __float_as_int(idf.y), __float_as_int(idf.z), __float_as_int(idf.w));
         const float2 hr = make_float2(hf.x, hf.y);
         // The path's throughput T rides in the three spare words of the two state elements.  Its radiance so far needs no
@@ -483,6 +499,8 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
     static const int refill_env = [] { const char *e = getenv("RTOW_WF_REFILL"); return e ? atoi(e) : -1; }();
     const int refill = refill_env >= 0 ? refill_env : (S.fast_n_nodes >= 4096 ? 28 : 1);
     static const int leaf_min = [] { const char *e = getenv("RTOW_TRACE_LEAFMIN"); return e ? atoi(e) : 8; }();
+    static const int static_env = [] { const char *e = getenv("RTOW_WF_STATIC_CLAIM"); return e ? atoi(e) : 0; }();
+    const int static_claim = static_env && refill == 1 ? 1 : 0;
     // BVH scenes: 5 blocks x 96 registers (the traversal state stays in registers); list scenes run the reference list
     // walk, which is call-heavy rather than state-heavy: 8 blocks x 64 registers measured 6 % faster (smoke scene)
     static const int minb_env = [] { const char *e = getenv("RTOW_WF_MINB"); return e ? atoi(e) : 0; }();   // tuning knob
@@ -539,8 +557,8 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
         if (sampled) cudaEventRecord(ev[0], stream);
         if (fast) {
             const unsigned blocks = (unsigned)std::max<long long>(1, std::min<long long>((extend_bound + 127) / 128, (long long)sms * std::max(per_sm_bvh, 1)));
-            if (minb >= 8) wf_extend_kernel<8><<<blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, debug_exact_every);
-            else wf_extend_kernel<5><<<blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, debug_exact_every);
+            if (minb >= 8) wf_extend_kernel<8><<<blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, debug_exact_every, static_claim);
+            else wf_extend_kernel<5><<<blocks, 128, 0, stream>>>(S, W, parity, refill, leaf_min, debug_exact_every, static_claim);
         } else if (use_list) {
             const unsigned blocks = (unsigned)std::max<long long>(1, std::min<long long>((extend_bound + 127) / 128, (long long)sms * 8 * 4));
             wf_extend_list_kernel<<<blocks, 128, 0, stream>>>(S, W, parity);
