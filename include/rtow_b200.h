@@ -235,6 +235,10 @@ typedef struct rtow_stats {
 } rtow_stats;
 
 typedef struct rtow_scene rtow_scene;   /* opaque: device copies of the arrays above */
+/* Concurrency: a scene handle serves ONE call at a time.  Its entry points share per-scene work memory, counters and
+ * timing events (the trace entries, the render entries and rtow_stream_stats all use them), so two calls on the same handle
+ * that overlap -- from two host threads or on two streams -- corrupt each other's counters or queues.  Different handles
+ * (also on the same device) are independent; rtow_multi_* keeps one handle per shard for exactly that reason. */
 
 /* ---- entry points ---------------------------------------------------------- */
 

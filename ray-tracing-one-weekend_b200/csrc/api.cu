@@ -34,13 +34,20 @@ struct rtow_scene {
     WavefrontLaunch wf;
     int wf_pool = 0; size_t wf_pixels = 0;
     std::vector<void *> wf_allocs;
-    unsigned long long *wf_sq = nullptr; size_t wf_sq_pixels = 0;   // Q43.20 sums of squares (rtow_render_accumulate_moments_device)
+    unsigned long long *wf_sq = nullptr; size_t wf_sq_pixels = 0;   // Q33.30 sums of squares (rtow_render_accumulate_moments_device)
     unsigned long long *h_pinned = nullptr;
     bool pending_wavefront = false; uint64_t pending_paths = 0;
     WavefrontProfile wf_prof;
 };
 
 namespace {
+
+// CUDA events of one call, destroyed on every way out
+struct EventPair {
+    cudaEvent_t a = nullptr, b = nullptr;
+    cudaError_t create() { cudaError_t e = cudaEventCreate(&a); return e != cudaSuccess ? e : cudaEventCreate(&b); }
+    ~EventPair() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+};
 
 #define CUDA_TRY(expr)                                                                                         \
     do {                                                                                                       \
@@ -108,11 +115,41 @@ int validate(const rtow_scene_desc *d) {
     }
     if (d->top_kind == RTOW_TOP_BVH) {
         if (d->root_node < 0 || d->root_node >= d->n_nodes) return bad("root_node out of range");
+        // a tree, not a DAG: every node and every object has at most one parent (a shared subtree would be expanded once per
+        // path to it -- exponential -- and the tie rule below needs each leaf at one place in the in-order)
+        std::vector<uint8_t> node_refs((size_t)d->n_nodes, 0), obj_refs((size_t)d->n_objects, 0);
         for (int i = 0; i < d->n_nodes; ++i) {
             const rtow_bvh_node &n = d->nodes[i];
             for (int c : {n.left, n.right}) {
                 if (c >= 0 ? c >= d->n_nodes : ~c >= d->n_objects) return bad("bvh child out of range");
                 if (c >= 0 && c <= i) return bad("bvh nodes must be numbered parent-first");   // also rules out cycles
+            }
+            if (n.left >= 0 && n.left == n.right) return bad("bvh node with the same subtree as both children");
+            const int kids[2] = {n.left, n.right};
+            for (int k = 0; k < 2; ++k) {
+                const int c = kids[k];
+                if (k == 1 && c == n.left && c < 0) continue;     // the n == 1 node's second mention of its leaf
+                uint8_t &r = c >= 0 ? node_refs[(size_t)c] : obj_refs[(size_t)~c];
+                if (r) return bad("bvh node or object referenced by more than one parent (the structure must be a tree)");
+                r = 1;
+            }
+        }
+        if (node_refs[(size_t)d->root_node]) return bad("root_node is somebody's child");
+        // Equal hit distances go to the later leaf of the reference's left-then-right recursion (bvhNode.h:74-77); the
+        // traversals implement that as "larger object id wins", so object ids must increase along the in-order.
+        {
+            std::vector<int> stack{d->root_node};
+            int last = -1;
+            while (!stack.empty()) {
+                const int c = stack.back(); stack.pop_back();
+                if (c < 0) {
+                    if (~c <= last) return bad("bvh leaves must be numbered in in-order (flatten.h does; the tie rule of bvhNode.h:74-77 depends on it)");
+                    last = ~c;
+                    continue;
+                }
+                const rtow_bvh_node &n = d->nodes[c];
+                if (!(n.right == n.left && n.left < 0)) stack.push_back(n.right);
+                stack.push_back(n.left);
             }
         }
     }
@@ -263,6 +300,7 @@ int check_render_args(const rtow_scene *s, const rtow_camera *cam, const rtow_re
     L->pixel_count = rows * p->width;
     L->sky_gain = p->sky_gain; L->ambient_gain = p->ambient_gain;
     L->seed = p->seed;
+    L->vmax = sample_vmax(count);
     return RTOW_OK;
 }
 
@@ -578,8 +616,9 @@ int rtow_trace_rays(rtow_scene *s, const rtow_ray *rays, uint64_t n, rtow_hit *h
     if (int rc = resolve_traverse(s, traverse, &trav)) return rc;
     CUDA_TRY(cudaSetDevice(s->device));
     if (int rc = ensure_ray_buffers(s, n)) return rc;
-    cudaEvent_t t0, t1;
-    CUDA_TRY(cudaEventCreate(&t0)); CUDA_TRY(cudaEventCreate(&t1));
+    EventPair ev;
+    CUDA_TRY(ev.create());
+    const cudaEvent_t t0 = ev.a, t1 = ev.b;
     cudaStream_t st = s->stream;
     CUDA_TRY(cudaEventRecord(t0, st));
     CUDA_TRY(cudaMemcpyAsync(s->d_rays, rays, n * sizeof(rtow_ray), cudaMemcpyHostToDevice, st));
@@ -595,7 +634,6 @@ int rtow_trace_rays(rtow_scene *s, const rtow_ray *rays, uint64_t n, rtow_hit *h
         cudaEventElapsedTime(&stats->kernel_ms, s->ev0, s->ev1);
         cudaEventElapsedTime(&stats->total_ms, t0, t1);
     }
-    cudaEventDestroy(t0); cudaEventDestroy(t1);
     return RTOW_OK;
 }
 
@@ -742,8 +780,9 @@ int rtow_render(rtow_scene *s, const rtow_camera *cam, const rtow_render_params 
     const size_t pixels = (size_t)L.pixel_count;        // the whole frame, or the requested band of rows (outputs are band-sized)
     if (int rc = ensure_image_buffers(s, pixels)) return rc;
     cudaStream_t st = s->stream;
-    cudaEvent_t t0, t1;
-    CUDA_TRY(cudaEventCreate(&t0)); CUDA_TRY(cudaEventCreate(&t1));
+    EventPair ev;
+    CUDA_TRY(ev.create());
+    const cudaEvent_t t0 = ev.a, t1 = ev.b;
     CUDA_TRY(cudaEventRecord(t0, st));
     CUDA_TRY(cudaMemsetAsync(s->d_accum, 0, pixels * 3 * sizeof(float), st));
     if (int rc = rtow_render_accumulate_device(s, cam, params, s->d_accum, st)) return rc;
@@ -760,7 +799,6 @@ int rtow_render(rtow_scene *s, const rtow_camera *cam, const rtow_render_params 
         cudaEventElapsedTime(&stats->total_ms, t0, t1);
         stats->launches = tmp.launches + 1;
     }
-    cudaEventDestroy(t0); cudaEventDestroy(t1);
     return RTOW_OK;
 }
 

@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(256) render_mega_kernel(DScene S, rtow_camera 
                 alive = false;
             }
         }
-        if (!alive) { acc[0] += Lr[0]; acc[1] += Lr[1]; acc[2] += Lr[2]; }
+        if (!alive) { acc[0] += sample_channel(Lr[0], L.vmax); acc[1] += sample_channel(Lr[1], L.vmax); acc[2] += sample_channel(Lr[2], L.vmax); }      // same rule as the wavefront path
     }
 
     // fixed-order reduction over the S lanes of a pixel

@@ -5,6 +5,14 @@
 
 namespace rtow {
 
+// What a sample may add to a pixel, identically in both render kernels: a NaN adds nothing (the reference's behaviour there is
+// undefined, main.cpp:963), and a channel is clamped to +-vmax, vmax = min(1e9, 2^30 / samples of this call), so that the
+// wavefront path's Q31.32 pixel sums cannot wrap whatever the scene emits.  No reference scene comes near either limit.
+__device__ __forceinline__ float sample_channel(float v, float vmax) {
+    return v == v ? fminf(fmaxf(v, -vmax), vmax) : 0.f;
+}
+inline float sample_vmax(int sample_count) { return fminf(1e9f, 1073741824.f / (float)(sample_count > 0 ? sample_count : 1)); }
+
 struct RenderLaunch {
     int32_t width, height;
     int32_t sample_begin, sample_count;   // this launch: samples [begin, begin+count)
@@ -16,6 +24,7 @@ struct RenderLaunch {
     int32_t pixel_begin, pixel_count;     // this launch renders full-frame pixels [pixel_begin, +pixel_count) = a band of rows;
                                           // accumulators are indexed by pixel - pixel_begin
     uint64_t seed;
+    float vmax;                           // sample_vmax(sample_count)
 };
 
 // counters (RTOW_N_COUNTERS u64): [0] rays (world->hit queries) [1] paths [2] node visits [3] prim tests
@@ -53,7 +62,7 @@ struct WavefrontLaunch {
     int *queue;                           // RTOW_WF_MAX_CLASSES x pool entry indices of `in`, by shading class
     unsigned *counts;                     // 2 x RTOW_WF_MAX_CLASSES queue lengths (double-buffered by bounce parity)
     unsigned long long *fixed;            // W*H*3 radiance sums, Q31.32
-    unsigned long long *fixed_sq;         // W*H*3 sums of squared per-sample radiance, Q43.20; null unless moments were asked for
+    unsigned long long *fixed_sq;         // W*H*3 sums of squared per-sample radiance, Q33.30; null unless moments were asked for
     unsigned long long *control;          // [0] next work item [1] dead slots [2] extend queue head [3] rays traced
     unsigned long long *next_item, *dead_slots, *extend_head, *stats;
 };

@@ -29,7 +29,7 @@
 namespace rtow {
 
 #define WF_FIXED_SCALE 4294967296.0   // 2^32: radiance sums in Q31.32
-#define WF_FIXED_SQ_SCALE 1048576.0   // 2^20: sums of squares in Q43.20
+#define WF_FIXED_SQ_SCALE 1073741824.0   // 2^30: sums of squares in Q33.30 (a square below 1e-9 -- radiance 3e-5 -- rounds to 0)
 
 // 256-bit global accesses (LDG.E.256 / STG.E.256); p must be 32-byte aligned
 __device__ __forceinline__ void ld256(const void *p, float4 &a, float4 &b) {
@@ -355,12 +355,15 @@ __global__ void __launch_bounds__(128, 8) wf_extend_list_kernel(DScene S, Wavefr
 __device__ __forceinline__ void wf_add_pixel(const WavefrontLaunch &W, int pixel, const float L[3]) {
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const float v = L[k];
-        if (v != 0.f && fabsf(v) <= 1e9f) {    // NaN / inf / absurd radiance never reaches the sum (reference: undefined, main.cpp:963)
-            // v * 2^32 is exact in fp32 (|v| <= 1e9 < 2^30), so the float conversion rounds the same real number the double one did
+        const float v = sample_channel(L[k], W.L.vmax);     // NaN -> 0, |v| <= vmax: the sum of a call's samples stays below 2^31
+        if (v != 0.f) {
+            // v * 2^32 is exact in fp32 (a power-of-two scale), so the float conversion rounds the same real number the double one did
             atomicAdd(&W.fixed[(size_t)(pixel - W.L.pixel_begin) * 3 + k], (unsigned long long)__float2ll_rn(v * (float)WF_FIXED_SCALE));
-            if (W.fixed_sq && fabsf(v) <= 1e6f)
-                atomicAdd(&W.fixed_sq[(size_t)(pixel - W.L.pixel_begin) * 3 + k], (unsigned long long)__double2ll_rn((double)v * (double)v * WF_FIXED_SQ_SCALE));
+            if (W.fixed_sq) {
+                // squares: clamped so that a call's sum stays below 2^32 (Q33.30); variance estimates saturate beyond that
+                const double sq = fmin((double)v * (double)v, 4294967296.0 / (double)W.L.sample_count);
+                atomicAdd(&W.fixed_sq[(size_t)(pixel - W.L.pixel_begin) * 3 + k], (unsigned long long)__double2ll_rn(sq * WF_FIXED_SQ_SCALE));
+            }
         }
     }
 }

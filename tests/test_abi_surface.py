@@ -190,3 +190,42 @@ def test_cli_fails_loudly_without_a_device(pkg):
         pytest.skip("a CUDA device is visible")
     out = subprocess.run([cli, "--scene", "cornell_ned", "--width", "8", "--height", "8", "--spp", "1"], capture_output=True, text=True)
     assert out.returncode == 3 and "no CPU path" in out.stderr
+
+
+def test_scene_create_rejects_a_dag_and_out_of_order_leaves(pkg, abi):
+    """rtow_scene_create validates before it touches a device: a BVH given as a DAG (a node or object under two parents) or with
+    leaves not numbered along the in-order (the tie rule of bvhNode.h:74-77 is implemented as 'larger object id wins') is
+    RTOW_ERR_INVALID_ARG.  A well-formed scene passes validation and fails later only for want of a device (on CPU boxes)."""
+    host = pkg.HostScene("bvh_stress", seed=5, n=9)
+    base = host.arrays()["nodes"].copy()
+    assert len(base) >= 4
+
+    def create(nodes):
+        d = abi.SceneDesc.from_buffer_copy(bytes(host.desc))      # a private copy of the POD (pointers to the scene's arrays included)
+        keep = np.ascontiguousarray(nodes)
+        d.nodes = keep.ctypes.data
+        h = C.c_void_p()
+        rc = pkg.lib().rtow_scene_create(C.byref(d), 0, C.byref(h))
+        msg = pkg.lib().rtow_last_error().decode()
+        if h:
+            pkg.lib().rtow_scene_destroy(h)
+        return rc, msg
+
+    rc, msg = create(base)
+    assert rc in (abi.OK, abi.ERR_NO_DEVICE), msg
+    internal = [i for i in range(len(base)) if base["left"][i] >= 0 and base["right"][i] >= 0]
+    dag = base.copy()
+    i = internal[0]
+    dag["right"][i] = dag["left"][i]                    # both children the same subtree
+    rc, msg = create(dag)
+    assert rc == abi.ERR_INVALID_ARG, msg
+    dag = base.copy()
+    leaf_nodes = [i for i in range(len(base)) if base["left"][i] < 0 and base["right"][i] < 0 and base["left"][i] != base["right"][i]]
+    a, b = leaf_nodes[0], leaf_nodes[-1]
+    dag["right"][b] = dag["left"][a]                    # one object under two parents
+    rc, msg = create(dag)
+    assert rc == abi.ERR_INVALID_ARG and ("more than one parent" in msg or "in-order" in msg), msg
+    swapped = base.copy()
+    swapped["left"][a], swapped["right"][a] = base["right"][a], base["left"][a]      # leaves out of in-order
+    rc, msg = create(swapped)
+    assert rc == abi.ERR_INVALID_ARG and "in-order" in msg, msg
