@@ -51,6 +51,17 @@ __device__ __forceinline__ void st256(void *p, const float4 &a, const float4 &b)
 // NaNs are 0x7fffffff), so the extend kernels decide "dead" from the 32 bytes they load anyway; the ids keep depth = -1 too.
 #define WF_DEAD_BITS ((int)0xffffdead)
 
+// -DRTOW_WF_CHECK (tools/wf_check.sh): every queue / stream / pixel index is checked against its array before use and the
+// host checks the counters' invariants after the drain.  compute-sanitizer is closed on the GPU pool this was developed on
+// (profiles/r02_sanitizer_unavailable.txt); this build is what stands in for its memcheck pass.  A violation prints one line
+// (no trap: the context stays usable) and skips the access.
+#ifdef RTOW_WF_CHECK
+#include <cstdio>
+#define WF_CHECK(cond, what, a, b) ((cond) ? true : (printf("WF_CHECK violation: %s (%lld, %lld) block %d thread %d\n", what, (long long)(a), (long long)(b), (int)blockIdx.x, (int)threadIdx.x), false))
+#else
+#define WF_CHECK(cond, what, a, b) (true)
+#endif
+
 #define WF_SAMPLE_BLOCK 64
 __device__ __forceinline__ void wf_item_to_pixel(const WavefrontLaunch &W, unsigned long long item, int &pixel, int &sample) {
     // Order of the work items: blocks of WF_SAMPLE_BLOCK sample indices; inside a block, groups of 32 neighbouring
@@ -87,6 +98,7 @@ __device__ __forceinline__ bool wf_start_path(const WavefrontLaunch &W, const rt
     int pixel, s;
     wf_item_to_pixel(W, item, pixel, s);
     if (pixel >= W.L.pixel_count) return false;
+    if (!WF_CHECK(pixel >= 0 && s >= 0 && s < W.L.sample_count && (unsigned)slot < (unsigned)W.pool, "start_path: pixel / sample / entry", pixel, s)) return false;
     pixel += W.L.pixel_begin;             // full-frame pixel index: camera sample position and Philox key
     const int x = pixel % W.L.width, y = pixel / W.L.width;
     const int row = W.L.height - 1 - y;
@@ -165,7 +177,9 @@ __device__ __forceinline__ void wf_enqueue(const WavefrontLaunch &W, unsigned *c
         unsigned base = 0;
         if (lane == leader) base = atomicAdd(&counts[cls], (unsigned)__popc(same));
         base = __shfl_sync(same, base, leader);
-        W.queue[(size_t)cls * W.pool + base + __popc(same & ((1u << lane) - 1u))] = slot;
+        const unsigned at = base + __popc(same & ((1u << lane) - 1u));
+        if (WF_CHECK(cls < RTOW_WF_MAX_CLASSES && at < (unsigned)W.pool && (unsigned)slot < (unsigned)W.pool, "enqueue: class / queue index / entry", cls, at))
+            W.queue[(size_t)cls * W.pool + at] = slot;
     }
 }
 
@@ -355,6 +369,7 @@ __global__ void __launch_bounds__(128, 8) wf_extend_list_kernel(DScene S, Wavefr
 __device__ __forceinline__ void wf_add_pixel(const WavefrontLaunch &W, int pixel, const float L[3]) {
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
+        if (!WF_CHECK(pixel >= W.L.pixel_begin && pixel < W.L.pixel_begin + W.L.pixel_count, "add_pixel: pixel outside the band", pixel, W.L.pixel_begin)) return;
         const float v = sample_channel(L[k], W.L.vmax);     // NaN -> 0, |v| <= vmax: the sum of a call's samples stays below 2^31
         if (v != 0.f) {
             // v * 2^32 is exact in fp32 (a power-of-two scale), so the float conversion rounds the same real number the double one did
@@ -409,6 +424,7 @@ __global__ void __launch_bounds__(256, 4) wf_shade_kernel(DScene S, WavefrontLau
     const unsigned cls_start = __shfl_sync(full, endc, cls > 0 ? cls - 1 : 0);
     int slot = -1;
     if (valid) slot = W.queue[(size_t)cls * W.pool + (j - (cls ? cls_start : 0u))];
+    if (valid && !WF_CHECK((unsigned)slot < (unsigned)W.pool && j < (unsigned)W.pool && cls < RTOW_WF_MAX_CLASSES, "shade: queued entry / out entry / class", slot, j)) return;
     float4 a, b, idf, hf;
     if (valid) {
         ld256(W.ray_in + 2 * (size_t)slot, a, b);
@@ -612,6 +628,17 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
         cudaEventSynchronize(ev[2]);
         cudaEventElapsedTime(&prof->tail_ms, ev[3], ev[2]);
     }
+#ifdef RTOW_WF_CHECK
+    {   // invariants after the drain: every work item handed out, every entry dead exactly once, rays >= paths
+        unsigned long long c[4];
+        cudaMemcpyAsync(c, W.control, sizeof c, cudaMemcpyDeviceToHost, stream);
+        cudaStreamSynchronize(stream);
+        const unsigned long long paths = (unsigned long long)W.L.pixel_count * (unsigned)W.L.sample_count;
+        if (c[0] < W.total_items || c[1] != (unsigned long long)W.pool || c[3] < paths)
+            fprintf(stderr, "WF_CHECK violation (host): items %llu of %llu, dead %llu of %d, rays %llu for %llu paths\n", c[0], W.total_items, c[1], W.pool, c[3], paths);
+        else fprintf(stderr, "WF_CHECK ok: %llu items, pool %d, %u iterations, %llu rays\n", W.total_items, W.pool, iters, c[3]);
+    }
+#endif
     wf_finalize_kernel<<<(unsigned)((n_acc + 255) / 256), 256, 0, stream>>>(W.fixed, d_accum, n_acc, 1.0 / WF_FIXED_SCALE);
     launches++;
     if (W.fixed_sq && d_accum_sq) {
