@@ -348,7 +348,7 @@ typedef struct rtow_render_profile_t {
     uint32_t tail_iterations;       /* bounce iterations after the last work item was handed out (the drain of the stream) */
     uint32_t polls;                 /* host synchronisations that looked at the device's progress counters */
     float tail_ms;                  /* device time from the poll that first saw the work exhausted to the end of the drain */
-    uint32_t reserved;
+    uint32_t finish_launches;       /* 1: the last paths were run to their ends by one wf_finish_kernel launch */
 } rtow_render_profile_t;
 int rtow_render_profile(rtow_scene *scene, rtow_render_profile_t *out);
 

@@ -138,7 +138,7 @@ class RenderProfile(C.Structure):
         ("tail_iterations", C.c_uint32),
         ("polls", C.c_uint32),
         ("tail_ms", C.c_float),
-        ("reserved", C.c_uint32),
+        ("finish_launches", C.c_uint32),
     ]
 
 

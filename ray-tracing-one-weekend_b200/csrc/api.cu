@@ -758,7 +758,7 @@ int rtow_render_profile(rtow_scene *s, rtow_render_profile_t *out) {
     if (s->pending_wavefront) {
         out->iterations = s->wf_prof.iterations; out->pool_slots = s->wf_prof.pool; out->sampled_iterations = s->wf_prof.samples;
         out->extend_ms_sum = s->wf_prof.extend_ms; out->shade_ms_sum = s->wf_prof.shade_ms;
-        out->tail_iterations = s->wf_prof.tail_iterations; out->polls = s->wf_prof.polls; out->tail_ms = s->wf_prof.tail_ms;
+        out->tail_iterations = s->wf_prof.tail_iterations; out->polls = s->wf_prof.polls; out->tail_ms = s->wf_prof.tail_ms; out->finish_launches = s->wf_prof.finish_launches;
     }
     return RTOW_OK;
 }

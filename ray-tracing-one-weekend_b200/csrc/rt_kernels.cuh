@@ -72,6 +72,7 @@ struct WavefrontProfile {
     uint32_t samples = 0, iterations = 0, pool = 0;
     uint32_t tail_iterations = 0;         // bounce iterations after the last work item was handed out (the drain)
     uint32_t polls = 0;                   // host synchronisations that looked at the device's progress counters
+    uint32_t finish_launches = 0;         // 1 if the last paths were run to their ends by wf_finish_kernel
     float tail_ms = 0.f;                  // device time of the drain (first poll that saw the work exhausted -> end)
 };
 cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaunch &W, float *d_accum, float *d_accum_sq, unsigned long long *h_pinned,

@@ -503,6 +503,87 @@ __global__ void __launch_bounds__(256, 4) wf_shade_kernel(DScene S, WavefrontLau
     wf_refill(W, cam, ended, (int)j, dead, early, early_base);      // the successor of an ended path starts in out[j]
 }
 
+// ---- finish: the last few paths run to their ends in one launch ------------------------------------------------------
+// Once the work items are exhausted the stream only drains: after a few bounces a handful of long paths (glass, the Cornell
+// box's depth-50 tails) is all that is left, and every further bounce costs two launches whose duration is one ray's chain
+// of memory round trips (~40 us per bounce, measured: 45 such iterations = 2 ms per frame, the fixed cost that capped 8-GPU
+// scaling in round 1).  When at most `finish_below` entries are alive the host launches this kernel instead: one thread per
+// entry, the megakernel's bounce loop (kernels.cu render_mega_kernel: same headers, same arithmetic, same Philox draws)
+// from the stored state to the path's end.  No successors: there is no work left to start.
+__global__ void __launch_bounds__(128) wf_finish_kernel(DScene S, WavefrontLaunch W, int parity) {
+    __shared__ PerlinSmem perlin;
+    perlin_stage(S, &perlin);
+    __syncthreads();
+    const unsigned full = 0xffffffffu;
+    const unsigned n = wf_entries(W, parity);
+    const bool use_fast = W.L.traverse == RTOW_TRAVERSE_FAST && S.fast_nodes != nullptr;
+    unsigned long long rays = 0, ended = 0;
+    for (unsigned j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+        float4 a, b, idf, hf;
+        ld256(W.ray_in + 2 * (size_t)j, a, b);
+        if (__float_as_int(b.w) == WF_DEAD_BITS) continue;
+        ld256(W.idh_in + 2 * (size_t)j, idf, hf);
+        Ray r;
+        r.ox = a.x; r.oy = a.y; r.oz = a.z; r.time = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z;
+        float T[3] = {b.w, hf.z, hf.w};
+        float Lr[3] = {0.f, 0.f, 0.f};
+        const int pixel = __float_as_int(idf.x);
+        int depth = __float_as_int(idf.w);
+        Rng g;
+        rng_init(g, W.L.seed, (uint32_t)pixel, (uint32_t)__float_as_int(idf.y));
+        g.next = (uint32_t)__float_as_int(idf.z);
+        for (;;) {
+            // ---- color.h:12-59, iterative: L += T*E ; T *= A (render_mega_kernel's body) ----
+            g.bounce = (uint32_t)depth;
+            rays++;
+            Ray rl = r;
+            root_ray(S, rl);
+            float t; int pid; unsigned nv = 0, pt = 0;
+            const bool hit = use_fast ? closest_hit_fast<false>(S, rl, 0.001f, FLT_MAX, &g, t, pid, nv, pt) : closest_hit_exact<false>(S, rl, 0.001f, FLT_MAX, &g, t, pid, nv, pt);
+            if (!hit) {
+                if (W.L.global_illum_en) {
+                    if (depth < 1) {                                              // color.h:35-50
+                        float ux, uy, uz;
+                        unit3(r.dx, r.dy, r.dz, ux, uy, uz);
+                        float k = (float)(1.0 + (double)uz);
+                        float sky0 = (float)((double)k * 0.1), sky1 = (float)((double)k * 0.3), sky2 = (float)((double)k * 1.0);
+                        Lr[0] += T[0] * (W.L.sky_gain * sky0); Lr[1] += T[1] * (W.L.sky_gain * sky1); Lr[2] += T[2] * (W.L.sky_gain * sky2);
+                    } else {                                                      // color.h:52-54
+                        Lr[0] += T[0] * W.L.ambient_gain; Lr[1] += T[1] * W.L.ambient_gain; Lr[2] += T[2] * W.L.ambient_gain;
+                    }
+                }
+                break;
+            }
+            MatRec m = load_material(S, __ldg(&S.prims[pid * 5]).y);
+            Hit h;
+            prim_record(S, pid, rl, t, m.needs_uv != 0, h);
+            float em[3];
+            if (depth < W.L.max_depth) {
+                float atten[3], sd[3], stime;
+                float rd[3] = {r.dx, r.dy, r.dz};
+                const bool go = scatter(S, &perlin, m, h, rd, r.time, g, atten, sd, stime, em);
+                Lr[0] += T[0] * em[0]; Lr[1] += T[1] * em[1]; Lr[2] += T[2] * em[2];
+                if (!go) break;
+                T[0] *= atten[0]; T[1] *= atten[1]; T[2] *= atten[2];
+                r.ox = h.p[0]; r.oy = h.p[1]; r.oz = h.p[2];
+                r.dx = sd[0]; r.dy = sd[1]; r.dz = sd[2];
+                r.time = stime;
+                depth++;
+            } else {
+                if (m.type == RTOW_MAT_DIFFUSE_LIGHT) {                        // color.h:25-30
+                    texture_value(S, &perlin, m.tex, h.u, h.v, h.p, em);
+                    Lr[0] += T[0] * em[0]; Lr[1] += T[1] * em[1]; Lr[2] += T[2] * em[2];
+                }
+                break;
+            }
+        }
+        wf_add_pixel(W, pixel, Lr);
+        ended++;
+    }
+    for (int off = 16; off; off >>= 1) { rays += __shfl_down_sync(full, rays, off); ended += __shfl_down_sync(full, ended, off); }
+    if ((threadIdx.x & 31) == 0 && rays) { atomicAdd(&W.stats[0], rays); atomicAdd(W.dead_slots, ended); }
+}
+
 __global__ void wf_finalize_kernel(const unsigned long long *__restrict__ fixed, float *__restrict__ accum, size_t n, double inv_scale) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -566,8 +647,9 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
     if (prof) { for (auto &e : ev) cudaEventCreate(&e); *prof = WavefrontProfile(); }
     long long shade_bound = W.pool, extend_bound = W.pool;
     long long next_poll = W.total_items <= (unsigned long long)W.pool ? 0 : 7;
-    uint32_t tail_iters = 0, polls = 0, iters = 0;
+    uint32_t tail_iters = 0, polls = 0, iters = 0, finished = 0;
     bool exhausted = false;
+    static const long long finish_below = [] { const char *e = getenv("RTOW_WF_FINISH_BELOW"); return e ? atoll(e) : 32768ll; }();     // 0: drain by bounce iterations only
     for (long long it = 0;; ++it) {
         const bool poll = it >= next_poll;
         const bool sampled = prof && poll;       // timed just before a synchronisation point
@@ -611,11 +693,16 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
             next_poll = it + std::max<long long>(4, std::min<long long>(256, (long long)(0.7 * left)));
         } else {
             if (!exhausted && prof) cudaEventRecord(ev[3], stream);      // the drain starts (within a poll interval of) here
-            // Every path alive now ends within max_depth + 1 more bounces: those iterations are launched back to back with no
-            // look in between (a look empties the launch queue: ~50 us of bubbles each against ~10 us iterations); blocks
-            // beyond the shrinking stream exit at once.  Should anything be left after that, looks resume every 4 iterations.
-            next_poll = it + (exhausted ? 4 : (long long)W.L.max_depth + 2);
             exhausted = true;
+            const long long alive = (long long)W.pool - (long long)dead;
+            if (alive <= finish_below) {
+                // few enough paths left: they run to their ends in one launch (wf_finish_kernel) and the frame is complete
+                W.ray_in = W.ray_buf[cur]; W.idh_in = W.idh_buf[cur];
+                wf_finish_kernel<<<(unsigned)std::max<long long>(1, (alive + 127) / 128), 128, 0, stream>>>(S, W, parity);
+                launches++; finished = 1;
+                break;
+            }
+            next_poll = it + 4;        // bounces run 4 at a time between looks until then (blocks beyond the shrinking stream exit at once)
             // alive now = entries the NEXT shade pass processes; the next extend pass still reads the entries of this bounce
             // (alive before its shade pass retired some): bounded by what was alive at the previous look
             const long long live = (long long)W.pool - (long long)dead;
@@ -636,7 +723,7 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
         const unsigned long long paths = (unsigned long long)W.L.pixel_count * (unsigned)W.L.sample_count;
         if (c[0] < W.total_items || c[1] != (unsigned long long)W.pool || c[3] < paths)
             fprintf(stderr, "WF_CHECK violation (host): items %llu of %llu, dead %llu of %d, rays %llu for %llu paths\n", c[0], W.total_items, c[1], W.pool, c[3], paths);
-        else fprintf(stderr, "WF_CHECK ok: %llu items, pool %d, %u iterations, %llu rays\n", W.total_items, W.pool, iters, c[3]);
+        else fprintf(stderr, "WF_CHECK ok: %llu items, pool %d, %u iterations, %llu rays\n", W.total_items, W.pool, iters + finished, c[3]);
     }
 #endif
     wf_finalize_kernel<<<(unsigned)((n_acc + 255) / 256), 256, 0, stream>>>(W.fixed, d_accum, n_acc, 1.0 / WF_FIXED_SCALE);
@@ -648,7 +735,7 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
     if (launches_out) *launches_out = launches;
     if (prof) {
         prof->iterations = iters; prof->pool = (uint32_t)W.pool;
-        prof->tail_iterations = tail_iters; prof->polls = polls;
+        prof->tail_iterations = tail_iters; prof->polls = polls; prof->finish_launches = finished;
         for (auto &e : ev) cudaEventDestroy(e);
     }
     return cudaGetLastError();

@@ -48,7 +48,7 @@ def main():
     if pr.sampled_iterations:
         n = pr.sampled_iterations
         print(f"  wavefront: {pr.iterations} iterations, pool {pr.pool_slots}, extend {pr.extend_ms_sum / n:.3f} ms/it, "
-              f"shade {pr.shade_ms_sum / n:.3f} ms/it (sampled {n}); drain {pr.tail_iterations} iterations, {pr.tail_ms:.3f} ms; {pr.polls} polls", flush=True)
+              f"shade {pr.shade_ms_sum / n:.3f} ms/it (sampled {n}); drain {pr.tail_iterations} iterations, {pr.tail_ms:.3f} ms (finish kernel: {pr.finish_launches}); {pr.polls} polls", flush=True)
 
 
 if __name__ == "__main__":
