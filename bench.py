@@ -329,8 +329,10 @@ def run_product(args):
         trav_ops_per_ray = box_ops * wc.node_visits_per_ray + OPS_PRIM * wc.prim_tests_per_ray
         achieved_tops = prof.pool_slots * trav_ops_per_ray / (ext_ms * 1e-3) / 1e12
         # list scenes and EXACT traversal run the reference walk in its own kernel (wavefront.cu run_wavefront)
-        ext_name = "wf_extend_kernel" if wc.traverse == abi.TRAVERSE_FAST else "wf_extend_exact_kernel"
-        dom = {"kernel": ext_name, "kernel_ms": ext_ms, "launches_per_step": prof.iterations, "units_per_launch": prof.pool_slots,
+        ext_name = "wf_extend_kernel" if wc.traverse == abi.TRAVERSE_FAST else ("wf_extend_list_kernel" if args.scene.startswith("cornell") else "wf_extend_exact_kernel")
+        dom = {"drain": {"iterations_after_last_work_item": prof.tail_iterations, "ms": prof.tail_ms, "finish_kernel_launches": prof.finish_launches,
+                         "host_polls_per_step": prof.polls},
+               "kernel": ext_name, "kernel_ms": ext_ms, "launches_per_step": prof.iterations, "units_per_launch": prof.pool_slots,
                "ops_per_unit": trav_ops_per_ray, "share_of_step": ext_ms / (ext_ms + shade_ms), "shade_kernel_ms": shade_ms,
                "sampled_launches": prof.sampled_iterations}
         kernel_name = "wavefront"
@@ -350,12 +352,12 @@ def run_product(args):
     hbm_note = "accumulator read+write only: this kernel is not HBM-bound"
     traffic = None
     if dom["kernel"].startswith("wf_extend"):
-        # per launch and slot: ray 32 B + ids 16 B read, hit 8 B + queue entry 4 B written
-        alg_bytes = prof.pool_slots * (32 + 16 + 8 + 4)
+        # per launch and entry: ray record 32 B read, hit {t, prim} 8 B + queue entry 4 B written
+        alg_bytes = prof.pool_slots * (32 + 8 + 4)
         hbm_ach = alg_bytes / (dom["kernel_ms"] * 1e-3) / 1e9
-        hbm_note = dom["kernel"] + ": slot state read + hit/queue written per launch; the pool is partly L2-resident and the kernel is issue-bound, not HBM-bound"
+        hbm_note = dom["kernel"] + ": ray records read + hit/queue written per launch; the kernel is issue-bound, not HBM-bound"
         try:      # measured DRAM bytes per launch of the same kernel on the same scene and pool (one ncu --set full capture)
-            t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["wf_extend_kernel"]
+            t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[dom["kernel"]]
             if (W, H, args.scene) == (WIDTH, HEIGHT, SCENE) and prof.pool_slots == int(t.get("pool_slots", 1 << 20)):
                 traffic = int(t["dram_bytes_per_launch"])
         except Exception:

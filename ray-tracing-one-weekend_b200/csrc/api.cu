@@ -29,6 +29,9 @@ struct rtow_scene {
     void *d_rays = nullptr, *d_hits = nullptr; size_t ray_cap = 0;
     float *d_accum = nullptr, *d_rgb = nullptr; uint8_t *d_bgra = nullptr; size_t img_cap = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;             // second lane of rtow_trace_rays' copy / trace / copy pipeline
+    unsigned long long *d_counters2 = nullptr;  // its own work-queue head
+    cudaEvent_t ev_chunk = nullptr;
     bool has_fast = false;
     // wavefront path state (allocated on first use, regrown when the pool or the image grows)
     WavefrontLaunch wf;
@@ -398,6 +401,9 @@ void rtow_scene_destroy(rtow_scene *s) {
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->stream) cudaStreamDestroy(s->stream);
+    if (s->stream2) cudaStreamDestroy(s->stream2);
+    if (s->d_counters2) cudaFree(s->d_counters2);
+    if (s->ev_chunk) cudaEventDestroy(s->ev_chunk);
     delete s;
 }
 
@@ -619,19 +625,42 @@ int rtow_trace_rays(rtow_scene *s, const rtow_ray *rays, uint64_t n, rtow_hit *h
     EventPair ev;
     CUDA_TRY(ev.create());
     const cudaEvent_t t0 = ev.a, t1 = ev.b;
-    cudaStream_t st = s->stream;
-    CUDA_TRY(cudaEventRecord(t0, st));
-    CUDA_TRY(cudaMemcpyAsync(s->d_rays, rays, n * sizeof(rtow_ray), cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaEventRecord(s->ev0, st));
-    launch_trace(s->d, (const rtow_ray *)s->d_rays, n, (rtow_hit *)s->d_hits, trav, seed, s->d_counters, false, st);
-    CUDA_TRY(cudaGetLastError());
-    CUDA_TRY(cudaEventRecord(s->ev1, st));
-    CUDA_TRY(cudaMemcpyAsync(hits, s->d_hits, n * sizeof(rtow_hit), cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaEventRecord(t1, st));
-    CUDA_TRY(cudaStreamSynchronize(st));
+    // Copy in, trace, copy out, pipelined: the batch goes through in chunks of 2^20 rays on two streams, so that the PCIe
+    // copies of one chunk (36 B in, 48 B out per ray) run under the kernels of its neighbours; with pinned host buffers a
+    // large batch then costs about max(kernel time, copy time) instead of their sum.  Each stream has its own work-queue head.
+    if (!s->stream2) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&s->stream2, cudaStreamNonBlocking));
+        CUDA_TRY(cudaMalloc((void **)&s->d_counters2, RTOW_N_COUNTERS * sizeof(unsigned long long)));
+        CUDA_TRY(cudaMemset(s->d_counters2, 0, RTOW_N_COUNTERS * sizeof(unsigned long long)));
+        CUDA_TRY(cudaEventCreateWithFlags(&s->ev_chunk, cudaEventDisableTiming));
+    }
+    static const uint64_t chunk = [] { const char *e = getenv("RTOW_TRACE_CHUNK"); return e ? (uint64_t)atoll(e) : (1ull << 20); }();
+    const uint64_t n_chunks = chunk ? (n + chunk - 1) / chunk : 1;
+    cudaStream_t lanes[2] = {s->stream, s->stream2};
+    unsigned long long *heads[2] = {s->d_counters, s->d_counters2};
+    CUDA_TRY(cudaEventRecord(t0, lanes[0]));
+    CUDA_TRY(cudaStreamWaitEvent(lanes[1], t0, 0));
+    uint32_t launches = 0;
+    for (uint64_t k = 0; k < n_chunks; ++k) {
+        const uint64_t off = k * chunk, cnt = std::min<uint64_t>(chunk ? chunk : n, n - off);
+        cudaStream_t st = lanes[k & 1];
+        const rtow_ray *dr = (const rtow_ray *)s->d_rays + off;
+        rtow_hit *dh = (rtow_hit *)s->d_hits + off;
+        CUDA_TRY(cudaMemcpyAsync((void *)dr, rays + off, cnt * sizeof(rtow_ray), cudaMemcpyHostToDevice, st));
+        if (k == 0) CUDA_TRY(cudaEventRecord(s->ev0, st));
+        launch_trace(s->d, dr, cnt, dh, trav, seed, heads[k & 1], false, st, off);
+        CUDA_TRY(cudaGetLastError());
+        if (k == n_chunks - 1) CUDA_TRY(cudaEventRecord(s->ev1, st));
+        CUDA_TRY(cudaMemcpyAsync(hits + off, dh, cnt * sizeof(rtow_hit), cudaMemcpyDeviceToHost, st));
+        launches += 2;
+    }
+    CUDA_TRY(cudaEventRecord(s->ev_chunk, lanes[1]));
+    CUDA_TRY(cudaStreamWaitEvent(lanes[0], s->ev_chunk, 0));
+    CUDA_TRY(cudaEventRecord(t1, lanes[0]));
+    CUDA_TRY(cudaStreamSynchronize(lanes[0]));
     if (stats) {
-        stats->rays = n; stats->paths = 0; stats->launches = 1;
-        cudaEventElapsedTime(&stats->kernel_ms, s->ev0, s->ev1);
+        stats->rays = n; stats->paths = 0; stats->launches = launches;
+        cudaEventElapsedTime(&stats->kernel_ms, s->ev0, s->ev1);       // first kernel's start to the last kernel's end
         cudaEventElapsedTime(&stats->total_ms, t0, t1);
     }
     return RTOW_OK;

@@ -23,7 +23,9 @@ __device__ __forceinline__ bool closest_hit(const DScene &S, int traverse, const
 // ---- trace ------------------------------------------------------------------------------
 template <bool COUNT>
 __global__ void __launch_bounds__(256) trace_kernel(DScene S, const rtow_ray *__restrict__ rays, uint64_t n, rtow_hit *__restrict__ hits,
-                                                    int traverse, uint64_t seed, unsigned long long *__restrict__ counters) {
+                                                    int traverse, uint64_t seed, unsigned long long *__restrict__ counters, uint64_t first_index) {
+    // first_index: index of rays[0] in the caller's batch (rtow_trace_rays pipelines a batch in chunks); it only enters the
+    // Philox key of a medium's free-flight draw, so that a chunked batch gives the hits of an unchunked one
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     unsigned nv = 0, pt = 0;
     if (i < n) {
@@ -34,7 +36,7 @@ __global__ void __launch_bounds__(256) trace_kernel(DScene S, const rtow_ray *__
         r.time = __ldg(q + 6);
         float tmin = __ldg(q + 7), tmax = __ldg(q + 8);
         Rng g;
-        rng_init(g, seed, (uint32_t)i, (uint32_t)(i >> 32));
+        rng_init(g, seed, (uint32_t)(i + first_index), (uint32_t)((i + first_index) >> 32));
         root_ray(S, r);
         float t; int pid;
         float4 o0, o1, o2;
@@ -86,7 +88,7 @@ __global__ void __launch_bounds__(256) trace_kernel(DScene S, const rtow_ray *__
 template <bool COUNT, int MINB>
 __global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, const rtow_ray *__restrict__ rays, uint64_t n, rtow_hit *__restrict__ hits,
                                                                uint64_t seed, unsigned long long *__restrict__ counters,
-                                                               unsigned long long *__restrict__ queue_head, int refill_below, int leaf_min) {
+                                                               unsigned long long *__restrict__ queue_head, int refill_below, int leaf_min, uint64_t first_index) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     __shared__ uint2 s_stack[RTOW_TRACE_STACK_SMEM * 128];
@@ -98,7 +100,7 @@ __global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, c
     bool has_ray = false;
     bool more = true;             // the queue may still hold rays
     unsigned nv = 0, pt = 0;
-    const auto key_of = [&] { RngKey k; k.seed = seed; k.pixel = (uint32_t)idx; k.sample = (uint32_t)(idx >> 32); k.bounce = 0; return k; };
+    const auto key_of = [&] { RngKey k; k.seed = seed; k.pixel = (uint32_t)(idx + first_index); k.sample = (uint32_t)((idx + first_index) >> 32); k.bounce = 0; return k; };
 
     for (;;) {
         // 1. finished lanes park their result
@@ -166,7 +168,7 @@ __global__ void __launch_bounds__(128, MINB) trace_persistent_kernel(DScene S, c
 
 template <bool COUNT>
 __global__ void __launch_bounds__(256) trace_finish_kernel(DScene S, const rtow_ray *__restrict__ rays, uint64_t n, rtow_hit *__restrict__ hits,
-                                                           uint64_t seed, unsigned long long *__restrict__ counters) {
+                                                           uint64_t seed, unsigned long long *__restrict__ counters, uint64_t first_index) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     unsigned nv = 0, pt = 0;
     if (i < n) {
@@ -180,7 +182,7 @@ __global__ void __launch_bounds__(256) trace_finish_kernel(DScene S, const rtow_
         float t = res.x; int pid = __float_as_int(res.y);
         if (pid == RTOW_NEEDS_EXACT) {
             Rng g;
-            rng_init(g, seed, (uint32_t)i, (uint32_t)(i >> 32));
+            rng_init(g, seed, (uint32_t)(i + first_index), (uint32_t)((i + first_index) >> 32));
             if (!closest_hit_exact<COUNT>(S, r, __ldg(q + 7), __ldg(q + 8), &g, t, pid, nv, pt)) pid = -1;
         }
         float4 o0, o1, o2;
@@ -211,7 +213,7 @@ __global__ void __launch_bounds__(256) trace_finish_kernel(DScene S, const rtow_
 }
 
 void launch_trace(const DScene &S, const rtow_ray *d_rays, uint64_t n, rtow_hit *d_hits, int traverse, uint64_t seed,
-                  unsigned long long *d_counters, bool count, cudaStream_t stream) {
+                  unsigned long long *d_counters, bool count, cudaStream_t stream, uint64_t first_index) {
     if (n == 0) return;
     if (traverse == RTOW_TRAVERSE_FAST && S.fast_nodes) {
         // persistent warps: enough blocks to fill every SM at the kernel's occupancy, never more warps than rays/32
@@ -228,10 +230,10 @@ void launch_trace(const DScene &S, const rtow_ray *d_rays, uint64_t n, rtow_hit 
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, 0);
             unsigned long long want = (n + 127) / 128;
             unsigned blocks = (unsigned)std::min<unsigned long long>(want, (unsigned long long)sms * (unsigned)std::max(per_sm, 1));
-            kern<<<blocks, 128, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters, head, refill, leaf_min);
+            kern<<<blocks, 128, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters, head, refill, leaf_min, first_index);
             unsigned fb = (unsigned)((n + 255) / 256);
-            if (count) trace_finish_kernel<true><<<fb, 256, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters);
-            else trace_finish_kernel<false><<<fb, 256, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters);
+            if (count) trace_finish_kernel<true><<<fb, 256, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters, first_index);
+            else trace_finish_kernel<false><<<fb, 256, 0, stream>>>(S, d_rays, n, d_hits, seed, d_counters, first_index);
         };
         if (count) go(trace_persistent_kernel<true, 4>);
         else if (minb >= 8) go(trace_persistent_kernel<false, 8>);
@@ -241,8 +243,8 @@ void launch_trace(const DScene &S, const rtow_ray *d_rays, uint64_t n, rtow_hit 
         return;
     }
     unsigned blocks = (unsigned)((n + 255) / 256);
-    if (count) trace_kernel<true><<<blocks, 256, 0, stream>>>(S, d_rays, n, d_hits, traverse, seed, d_counters);
-    else trace_kernel<false><<<blocks, 256, 0, stream>>>(S, d_rays, n, d_hits, traverse, seed, d_counters);
+    if (count) trace_kernel<true><<<blocks, 256, 0, stream>>>(S, d_rays, n, d_hits, traverse, seed, d_counters, first_index);
+    else trace_kernel<false><<<blocks, 256, 0, stream>>>(S, d_rays, n, d_hits, traverse, seed, d_counters, first_index);
 }
 
 // ---- render: megakernel -----------------------------------------------------------------

@@ -32,7 +32,7 @@ struct RenderLaunch {
 // [8] work-queue head of the persistent kernels
 enum { RTOW_N_COUNTERS = 16, RTOW_COUNTER_QUEUE_HEAD = 8 };
 void launch_trace(const DScene &S, const rtow_ray *d_rays, uint64_t n, rtow_hit *d_hits, int traverse, uint64_t seed,
-                  unsigned long long *d_counters, bool count, cudaStream_t stream);
+                  unsigned long long *d_counters, bool count, cudaStream_t stream, uint64_t first_index = 0);
 void launch_render_mega(const DScene &S, const rtow_camera &cam, const RenderLaunch &L, float *d_accum,
                         unsigned long long *d_counters, bool count, cudaStream_t stream);
 // ---- wavefront path (wavefront.cu) --------------------------------------------------------------------------

@@ -95,3 +95,24 @@ def test_counters_match_oracle(gpu, abi, ob, port):
     # node (slab) tests are the reference's count exactly; an n==1 BvhNode tests its leaf twice in the reference
     # (bvhNode.h:38-40,70-71) and the oracle counts both, the kernel evaluates a non-medium leaf once (same answer)
     assert abs(g_nv - nv) < 1e-9 and 0 < g_pt <= pt + 1e-9
+
+
+def test_host_batches_are_pipelined_in_chunks_without_changing_hits(gpu, abi, ob):
+    """rtow_trace_rays sends a large host batch through in chunks of 2^20 rays on two streams (copies under kernels).  A medium's
+    free-flight draw is keyed by the ray's index in the WHOLE batch, so the chunked call must return exactly what one
+    unchunked launch over the same rays returns (rtow_trace_rays_device), media hits included."""
+    import torch
+    host = gpu.HostScene("cornell_smoke_ned", seed=12345, wrap=True)
+    dev = gpu.DeviceScene(host.desc)
+    n = (1 << 21) + 12345                        # three chunks, the last one ragged
+    rays = np.concatenate([ob.camera_rays(gpu.main_camera(640, 360), 640, 360, 1 << 20, seed=3), ob.incoherent_rays(n - (1 << 20), seed=4, extent=450.0)])
+    got, st = dev.trace(rays, seed=77)
+    assert st.rays == n
+    d_rays = torch.from_numpy(rays.view(np.uint8).reshape(n, -1).copy()).cuda()
+    d_hits = torch.empty(n, 48, dtype=torch.uint8, device="cuda:0")
+    dev.trace_device(d_rays.data_ptr(), n, d_hits.data_ptr(), abi.TRAVERSE_AUTO, 77, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    want = d_hits.cpu().numpy().view(abi.hit_dtype).reshape(-1)
+    mats = host.arrays()["materials"]
+    assert (mats["type"][np.maximum(want["mat_id"], 0)][want["mat_id"] >= 0] == abi.MAT_ISOTROPIC).sum() > 1000, "the batch must exercise media"
+    assert got.tobytes() == want.tobytes()
