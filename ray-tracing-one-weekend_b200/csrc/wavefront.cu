@@ -510,7 +510,7 @@ __global__ void __launch_bounds__(256, 4) wf_shade_kernel(DScene S, WavefrontLau
 // scaling in round 1).  When at most `finish_below` entries are alive the host launches this kernel instead: one thread per
 // entry, the megakernel's bounce loop (kernels.cu render_mega_kernel: same headers, same arithmetic, same Philox draws)
 // from the stored state to the path's end.  No successors: there is no work left to start.
-__global__ void __launch_bounds__(128) wf_finish_kernel(DScene S, WavefrontLaunch W, int parity) {
+__global__ void __launch_bounds__(128, 2) wf_finish_kernel(DScene S, WavefrontLaunch W, int parity) {
     __shared__ PerlinSmem perlin;
     perlin_stage(S, &perlin);
     __syncthreads();
