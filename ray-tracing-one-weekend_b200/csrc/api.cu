@@ -709,7 +709,11 @@ int rtow_render_accumulate_moments_device(rtow_scene *s, const rtow_camera *cam,
     }
     if (kernel == RTOW_KERNEL_WAVEFRONT) {
         // Synchronises `stream` internally (the host loop polls the pool for completion).
-        static const long long pool_cap = [] { const char *e = getenv("RTOW_WF_POOL"); return e ? atoll(e) : (1ll << 21); }();   // 2 M slots x 64 B: measured 1.4-2.6 % ahead of 1 M at full sample counts
+        // Entries in flight.  With the streaming design (two buffers, nothing meant to stay in L2) a longer stream only amortises
+        // the per-launch tails better: measured on B200 at 1024 spp of the configs[1] scene 2^20 / 2^21 / 2^22 / 2^23 / 2^24 / 2^25
+        // entries = 2762 / 3033 / 3179 / 3288 / 3333 / 3338 Mpaths/s, and at the 128 spp an 8-GPU shard renders 3003 (2^21) / 3228 /
+        // 3223 / 3155; Cornell + smoke 737 / 752 / 766 / 768 / 766 / 753.  Default 2^23 = 1 GB of state + 0.5 GB of queues.
+        static const long long pool_cap = [] { const char *e = getenv("RTOW_WF_POOL"); return e ? atoll(e) : (1ll << 23); }();
         const long long n_pixels = (long long)L.pixel_count;
         const unsigned long long items = (unsigned long long)((n_pixels + 31) / 32) * 32ull * (unsigned)L.sample_count;
         long long pool = (long long)std::min<unsigned long long>(items, (unsigned long long)pool_cap);
