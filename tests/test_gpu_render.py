@@ -288,6 +288,16 @@ def test_headless_cli_writes_ppm_pfm_and_stats(gpu, abi, tmp_path):
     host = gpu.HostScene("cornell_smoke_ned", seed=12345)
     img, _ = gpu.DeviceScene(host.desc).render(gpu.main_camera(64, 36), abi.default_render_params(64, 36, 8, seed=5))
     assert np.array_equal(img, rgb)
+    # --gpus N: the same frame through rtow_multi_render (as many GPUs as the box has, at most 2 here)
+    g = min(2, gpu.lib().rtow_device_count())
+    out = subprocess.run([cli, "--scene", "cornell_smoke_ned", "--width", "64", "--height", "36", "--spp", "8", "--seed", "5", "--out", prefix + "m",
+                          "--gpus", str(g)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    stm = json.loads(out.stdout.strip().splitlines()[-1])
+    assert stm["gpus"] == g and stm["paths"] == st["paths"] and stm["rays"] == st["rays"]
+    pfm = open(prefix + "m.pfm", "rb").read()
+    rgbm = np.frombuffer(pfm[len(b"PF\n64 36\n-1.0\n"):], dtype="<f4").reshape(36, 64, 3)[::-1]
+    assert np.abs(rgbm - rgb).max() <= 2e-5 * max(1.0, float(rgb.max()))
 
 
 @pytest.mark.parametrize("kernel", ["mega", "wavefront"])

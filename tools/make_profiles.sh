@@ -6,7 +6,7 @@ G=gpurun_out; P=profiles; T=/tmp/prof_$tag
 rm -rf $T; mkdir -p $T; ( cd $T && cuobjdump -xelf all $OLDPWD/ray-tracing-one-weekend_b200/csrc/librtow_b200.so > /dev/null && for f in *.cubin; do nvdisasm -g -c $f > ${f%.cubin}.sass 2>/dev/null; done )
 lines() { ncu -i $G/$1.ncu-rep --page source --csv > $T/$1.csv 2>/dev/null; python tools/ncu_lines.py $T/$1.csv $T/$2.sm_100a.sass $3 ${4:-30} ${5:-1}; }
 {
-  echo "ncu --set full --clock-control none --import-source on -k regex:<kernel> -s 60 -c 1 python tools/prof_render.py --scene random_ned --spp 128   ($tag; configs[1] scene with its 2048x1024 image texture, 1920x1080, full 64-sample blocks, stream of 2^21 entries of 64 B)"
+  echo "ncu --set full --clock-control none --import-source on -k regex:<kernel> -s 60 -c 1 python tools/prof_render.py --scene random_ned --spp 128   ($tag; configs[1] scene with its 2048x1024 image texture, 1920x1080, full 64-sample blocks, stream of 2^23 entries of 64 B)"
   python tools/ncu_summary.py $G/${tag}_extend.ncu-rep
   echo; echo "---- wf_extend_kernel: source lines (ncu SASS page joined with nvdisasm line info, tools/ncu_lines.py)"
   lines ${tag}_extend wavefront wf_extend_kernelILi5 30
@@ -61,10 +61,10 @@ def dram(rep):
     rd = float(r[h.index("dram__bytes_read.sum")]) * conv[units[h.index("dram__bytes_read.sum")]]
     wr = float(r[h.index("dram__bytes_write.sum")]) * conv[units[h.index("dram__bytes_write.sum")]]
     return int(rd), int(wr)
-t = {"_comment": "dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full --clock-control none captures summarised in profiles/${tag}_*_ncu_summary.txt (stream of 2^21 entries of 64 B). bench.py copies the dominant kernel's figure into roofline.traffic when it runs the same scene and stream size."}
+t = {"_comment": "dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full --clock-control none captures summarised in profiles/${tag}_*_ncu_summary.txt (stream of 2^23 entries of 64 B). bench.py copies the dominant kernel's figure into roofline.traffic when it runs the same scene and stream size."}
 for k, rep in (("wf_extend_kernel", "$G/${tag}_extend.ncu-rep"), ("wf_shade_kernel", "$G/${tag}_shade.ncu-rep"), ("wf_extend_list_kernel", "$G/${tag}_list.ncu-rep")):
     rd, wr = dram(rep)
-    t[k] = {"pool_slots": 2097152, "dram_bytes_per_launch": rd + wr, "read": rd, "written": wr}
+    t[k] = {"pool_slots": 8388608, "dram_bytes_per_launch": rd + wr, "read": rd, "written": wr}
 json.dump(t, open("$P/ncu_traffic.json", "w"), indent=2)
 print(json.dumps(t, indent=1)[:600])
 PY
