@@ -595,16 +595,21 @@ __global__ void wf_finalize_kernel(const unsigned long long *__restrict__ fixed,
 cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaunch &W, float *d_accum, float *d_accum_sq, unsigned long long *h_pinned,
                           cudaStream_t stream, uint32_t *launches_out, WavefrontProfile *prof) {
     // Lane refill pays when traversals are long (a million spheres: ~55 node visits per ray); on a scene of a few dozen
-    // nodes a ray takes ~3 steps and the refill's load latency would dominate, so a warp then simply runs batches of 32.
+    // nodes a ray takes ~3 steps and the refill's load latency would dominate, so a warp then runs (almost) whole batches of 32.
+    // (round 2, dense stream: on the small scene a refill below 8 live lanes, leaves only when no lane waits at a node, and
+    // 8 blocks x 64 registers measured 3335 against 3264 Mpaths/s with round 1's 1 / 8 / 5; on a million spheres the leaf rule
+    // alone costs 2x, so the big-tree defaults stay)
+    const bool small_tree = S.fast_n_nodes < 4096;
     static const int refill_env = [] { const char *e = getenv("RTOW_WF_REFILL"); return e ? atoi(e) : -1; }();
-    const int refill = refill_env >= 0 ? refill_env : (S.fast_n_nodes >= 4096 ? 28 : 1);
-    static const int leaf_min = [] { const char *e = getenv("RTOW_TRACE_LEAFMIN"); return e ? atoi(e) : 8; }();
+    const int refill = refill_env >= 0 ? refill_env : (small_tree ? 8 : 28);
+    static const int leaf_env = [] { const char *e = getenv("RTOW_TRACE_LEAFMIN"); return e ? atoi(e) : -1; }();
+    const int leaf_min = leaf_env >= 0 ? leaf_env : (small_tree ? 32 : 8);
     static const int static_env = [] { const char *e = getenv("RTOW_WF_STATIC_CLAIM"); return e ? atoi(e) : 0; }();
     const int static_claim = static_env && refill == 1 ? 1 : 0;
     // BVH scenes: 5 blocks x 96 registers (the traversal state stays in registers); list scenes run the reference list
     // walk, which is call-heavy rather than state-heavy: 8 blocks x 64 registers measured 6 % faster (smoke scene)
     static const int minb_env = [] { const char *e = getenv("RTOW_WF_MINB"); return e ? atoi(e) : 0; }();   // tuning knob
-    const int minb = minb_env ? minb_env : (S.fast_nodes ? 5 : 8);
+    const int minb = minb_env ? minb_env : (S.fast_nodes && !small_tree ? 5 : 8);
     static const int debug_exact_every = [] { const char *e = getenv("RTOW_WF_DEBUG_EXACT_EVERY"); return e ? atoi(e) : 0; }();   // tests: every n-th entry takes the in-kernel fallback to the reference walk
     static const int exact_minb = [] { const char *e = getenv("RTOW_WF_EXACT_MINB"); return e ? atoi(e) : 8; }();
     const bool fast = W.L.traverse == RTOW_TRAVERSE_FAST && S.fast_nodes != nullptr;
