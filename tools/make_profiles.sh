@@ -9,7 +9,7 @@ lines() { ncu -i $G/$1.ncu-rep --page source --csv > $T/$1.csv 2>/dev/null; pyth
   echo "ncu --set full --clock-control none --import-source on -k regex:<kernel> -s 60 -c 1 python tools/prof_render.py --scene random_ned --spp 128   ($tag; configs[1] scene with its 2048x1024 image texture, 1920x1080, full 64-sample blocks, stream of 2^23 entries of 64 B)"
   python tools/ncu_summary.py $G/${tag}_extend.ncu-rep
   echo; echo "---- wf_extend_kernel: source lines (ncu SASS page joined with nvdisasm line info, tools/ncu_lines.py)"
-  lines ${tag}_extend wavefront wf_extend_kernelILi5 30
+  lines ${tag}_extend wavefront wf_extend_kernelILi8 30
   echo; python tools/ncu_summary.py $G/${tag}_shade.ncu-rep
   echo; echo "---- wf_shade_kernel: source lines"
   lines ${tag}_shade wavefront wf_shade_kernel 30
