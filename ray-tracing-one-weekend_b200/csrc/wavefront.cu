@@ -62,7 +62,10 @@ __device__ __forceinline__ void st256(void *p, const float4 &a, const float4 &b)
 #define WF_CHECK(cond, what, a, b) (true)
 #endif
 
-#define WF_SAMPLE_BLOCK 64
+#ifndef WF_SAMPLE_BLOCK_LOG2
+#define WF_SAMPLE_BLOCK_LOG2 6
+#endif
+#define WF_SAMPLE_BLOCK (1 << WF_SAMPLE_BLOCK_LOG2)
 __device__ __forceinline__ void wf_item_to_pixel(const WavefrontLaunch &W, unsigned long long item, int &pixel, int &sample) {
     // Order of the work items: blocks of WF_SAMPLE_BLOCK sample indices; inside a block, groups of 32 neighbouring
     // pixels; inside a group, consecutive items are the 32 pixels of ONE sample index.  So the lanes of a warp start
@@ -78,8 +81,8 @@ __device__ __forceinline__ void wf_item_to_pixel(const WavefrontLaunch &W, unsig
         unsigned long long sb = (unsigned long long)__double2ll_rd((double)item * W.inv_block_items);
         unsigned long long j = item - sb * block_items;
         if ((long long)j < 0) { j += block_items; --sb; } else if (j >= block_items) { j -= block_items; ++sb; }
-        pixel = (int)((j >> 11) * 32ull + (j & 31ull));            // groups of 32 pixels x 64 samples = 2048 items
-        sample = (int)(sb * WF_SAMPLE_BLOCK + ((j & 2047ull) >> 5));
+        pixel = (int)((j >> (5 + WF_SAMPLE_BLOCK_LOG2)) * 32ull + (j & 31ull));            // groups of 32 pixels x 64 samples = 2048 items
+        sample = (int)(sb * WF_SAMPLE_BLOCK + ((j & ((32ull << WF_SAMPLE_BLOCK_LOG2) - 1ull)) >> 5));
         return;
     }
     const unsigned long long j = item - W.full_items;
