@@ -298,6 +298,12 @@ def test_headless_cli_writes_ppm_pfm_and_stats(gpu, abi, tmp_path):
     pfm = open(prefix + "m.pfm", "rb").read()
     rgbm = np.frombuffer(pfm[len(b"PF\n64 36\n-1.0\n"):], dtype="<f4").reshape(36, 64, 3)[::-1]
     assert np.abs(rgbm - rgb).max() <= 2e-5 * max(1.0, float(rgb.max()))
+    # the random scene through the CLI carries the reference's image texture (found next to the library, whatever the CWD)
+    if gpu.image_dir():
+        out = subprocess.run([cli, "--scene", "random_ned", "--width", "32", "--height", "18", "--spp", "2", "--out", prefix + "r"],
+                             capture_output=True, text=True, cwd=str(tmp_path))
+        assert out.returncode == 0, out.stderr
+        assert json.loads(out.stdout.strip().splitlines()[-1])["image_textures"] == 1
 
 
 @pytest.mark.parametrize("kernel", ["mega", "wavefront"])
