@@ -3,6 +3,7 @@
 //   rtow::DeviceWorld<RefTraits> gpu(world);            // flatten the object graph + rtow_scene_create, once
 //   rtow::Image frame;
 //   gpu.render(*mainCamera, params, frame);             // per frame: camera POD + rtow_render
+//   rtow::MultiDeviceWorld<RefTraits> gpus(world);      // the same on every GPU of the box (rtow_multi_*)
 //
 // replaces raytraceWorkerProcedure (main.cpp:876-1036: N threads, condvar hand-shake, color() per sample) for a scene
 // built with the reference's own classes (Traits names them) or with the mirror API of
@@ -83,6 +84,41 @@ private:
         if (rc != RTOW_OK) throw RenderError(rc, rtow_last_error());
     }
     rtow_scene *scene_ = nullptr;
+};
+
+// The same on every GPU of the box (or the listed ones): replaces the reference's worker-thread pool and column interleave
+// (main.cpp:182-195,936) with rtow_multi_* -- one host thread per GPU, samples per pixel split across them, one reduce +
+// resolve kernel over NVLink peer memory.  Same image as DeviceWorld up to fp32 summation order, for any device count.
+template <class Traits>
+class MultiDeviceWorld {
+public:
+    explicit MultiDeviceWorld(const typename Traits::Hitable *world, const std::vector<int32_t> &devices = {}) {
+        FlatScene flat;
+        flatten<Traits>(world, flat);
+        rtow_scene_desc desc = flat.desc();
+        check(rtow_multi_create(&desc, devices.empty() ? nullptr : devices.data(), (int32_t)devices.size(), &multi_));
+    }
+    ~MultiDeviceWorld() { rtow_multi_destroy(multi_); }
+    MultiDeviceWorld(const MultiDeviceWorld &) = delete;
+    MultiDeviceWorld &operator=(const MultiDeviceWorld &) = delete;
+
+    rtow_stats render(typename Traits::Camera &cam, const rtow_render_params &params, Image &out, bool dof_enabled = false) {
+        const rtow_camera pod = camera_pod<Traits>(cam, dof_enabled);
+        out.width = params.width;
+        out.height = params.row_count > 0 ? params.row_count : params.height;
+        out.rgb.resize((size_t)out.width * out.height * 3);
+        out.bgra.resize((size_t)out.width * out.height * 4);
+        rtow_stats st = {};
+        check(rtow_multi_render(multi_, &pod, &params, out.rgb.data(), out.bgra.data(), &st));
+        return st;
+    }
+    int devices() const { return rtow_multi_device_count(multi_); }
+
+private:
+    static void check(int rc) {
+        if (rc != RTOW_OK) throw RenderError(rc, rtow_last_error());
+    }
+    rtow_multi *multi_ = nullptr;
 };
 
 // One-shot form: flatten, upload, render, free.

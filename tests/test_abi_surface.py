@@ -155,6 +155,10 @@ rtow_stats frame(Hitable *world, Camera *cam, rtow::Image &out) {
     rtow::DeviceWorld<RefTraits> gpu(world);
     return gpu.render(*cam, rtow::default_params(800, 800, 64), out);
 }
+rtow_stats frame_on_all_gpus(Hitable *world, Camera *cam, rtow::Image &out) {
+    rtow::MultiDeviceWorld<RefTraits> gpus(world);      // main.cpp:182-195,936 -> one host thread per GPU behind the C ABI
+    return gpus.render(*cam, rtow::default_params(800, 800, 64), out);
+}
 """)
     r = subprocess.run(["g++", "-std=c++17", "-w", "-fsyntax-only", str(tu), "-I" + ref, "-I" + os.path.join(root, "include")], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
