@@ -483,6 +483,24 @@ int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out)
                 prog[4 * (size_t)i + 2] = make_float4(sn, cs, p.f[0], p.f[1]);
                 prog[4 * (size_t)i + 3] = make_float4(p.f[2], p.f[3], p.f[4], 0.f);
             }
+            // A medium whose boundary is a run of at most RTOW_LIST_BOX_MAX rectangles behind ONE wrapper chain (a Box, the case of
+            // every reference scene): flagged so that list_medium_t keeps the rectangles' plane distances of its first boundary
+            // query for the second one (constantMedium.h:32,36 ask the same boundary twice with different intervals).
+            for (int i = 0; i < desc->n_prims && ok; ++i) {
+                const rtow_prim &p = desc->prims[i];
+                if (p.type != RTOW_PRIM_MEDIUM || p.child_count < 1 || p.child_count > RTOW_LIST_BOX_MAX) continue;
+                bool run = true;
+                const uint32_t key0 = (uint32_t)dp[p.child_begin].xform_count >> 8;
+                for (int c = p.child_begin; c < p.child_begin + p.child_count; ++c) {
+                    const int t = desc->prims[c].type;
+                    if ((t != RTOW_PRIM_RECT_XY && t != RTOW_PRIM_RECT_XZ && t != RTOW_PRIM_RECT_YZ) || ((uint32_t)dp[c].xform_count >> 8) != key0) run = false;
+                }
+                if (run && key0 != RTOW_RAY_KEY_NONE) {
+                    int32_t w; std::memcpy(&w, &prog[4 * (size_t)i].x, 4);
+                    w |= RTOW_LIST_FLAG_BOX_RUN;
+                    std::memcpy(&prog[4 * (size_t)i].x, &w, 4);
+                }
+            }
             if (ok) {
                 if ((rc = upload(s, prog.data(), prog.size(), &D.list_prog))) return rc;
                 D.list_n = desc->n_prims;

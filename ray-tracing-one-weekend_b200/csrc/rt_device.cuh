@@ -385,6 +385,9 @@ __device__ __noinline__ bool object_hit(const DScene &S, const Ray r, float tmin
 #define RTOW_LIST_MAX 128
 #define RTOW_LIST_FORM_T 1
 #define RTOW_LIST_FORM_R 2
+#define RTOW_LIST_FLAG_BOX_RUN (1 << 10)   // medium record: the boundary is <= RTOW_LIST_BOX_MAX rectangles behind one wrapper chain (api.cu)
+#define RTOW_LIST_BOX_MAX 8
+#define RTOW_LIST_TT_STRIDE 128             // threads per block of wf_extend_list_kernel: one scratch column per thread
 __device__ __forceinline__ void list_xform(const Ray &r_in, int form, const float4 &q1, const float4 &q2, Ray &r) {
     r = r_in;
     if (form & RTOW_LIST_FORM_T) { r.ox = r.ox - q1.x; r.oy = r.oy - q1.y; r.oz = r.oz - q1.z; }          // hitable.h:53-55
@@ -404,7 +407,8 @@ __device__ __forceinline__ bool list_prim_t(const float4 *rec, int kind, const R
     return rect_t(q2.z, q2.w, q3.x, q3.y, q3.z, r.ox, r.dx, r.oy, r.dy, r.oz, r.dz, tmin, tmax, t_out);
 }
 // constantMedium.h:26-74 (medium_t above) on records
-static __device__ __noinline__ bool list_medium_t(const float4 *prog, int pid, const Ray r_in, float tmin, float tmax, const Rng *g, float &t_out) {
+// `tt`: this thread's column of a shared-memory scratch (entry i at tt[i * RTOW_LIST_TT_STRIDE]), see below
+static __device__ __noinline__ bool list_medium_t(const float4 *prog, int pid, const Ray r_in, float tmin, float tmax, const Rng *g, float *tt, float &t_out) {
     const float4 *rec = prog + 4 * pid;
     const float4 q0 = rec[0], q1 = rec[1];
     Ray r;
@@ -415,6 +419,49 @@ static __device__ __noinline__ bool list_medium_t(const float4 *prog, int pid, c
     int key = 0;
     Ray rr = r;
     float from = -FLT_MAX;
+#ifndef RTOW_NO_LIST_BOX_RUN
+    if (__float_as_int(q0.x) & RTOW_LIST_FLAG_BOX_RUN) {
+        // The boundary is a run of rectangles behind one wrapper chain (a Box).  constantMedium.h:32 and :36 ask it twice, with
+        // (-FLT_MAX, FLT_MAX) and (t1 + 0.0001, FLT_MAX); a rectangle's plane distance t = (k - o) / d and its in-bounds test
+        // (xy_rect.h:23-30) do not depend on the interval, so the first query keeps them -- t in shared memory, the bounds
+        // result as a bit -- and the second only replays the accept / narrow sequence of hitableList.h:26-34: no division, no
+        // transform, no point evaluation.  Same values, same order of decisions, NaN cases included (every comparison below
+        // is the one rect_t makes, on the same floats).
+        const float4 *c = prog + 4 * cb;
+        {
+            const float4 c0 = c[0];
+            const int ck = __float_as_int(c0.y);
+            if (ck != key) list_xform(r, (__float_as_int(c0.x) >> 8) & 3, c[1], c[2], rr);
+        }
+        unsigned inb = 0u;
+        bool any = false;
+        float closest = FLT_MAX;
+#pragma unroll 1
+        for (int i = 0; i < cn; ++i, c += 4) {
+            const int kind = __float_as_int(c[0].x) & 0xff;
+            const float4 q2 = c[2], q3 = c[3];
+            const bool xy = kind == RTOW_PRIM_RECT_XY, xz = kind == RTOW_PRIM_RECT_XZ;      // warp-uniform
+            const float oa = xy ? rr.oz : xz ? rr.oy : rr.ox, da = xy ? rr.dz : xz ? rr.dy : rr.dx;
+            const float o0 = (xy || xz) ? rr.ox : rr.oy, d0 = (xy || xz) ? rr.dx : rr.dy;
+            const float o1 = xy ? rr.oy : rr.oz, d1 = xy ? rr.dy : rr.dz;
+            const float t = (q3.z - oa) / da;
+            const float x = o0 + t * d0, y = o1 + t * d1;
+            const bool in = !(x < q2.z || x > q2.w || y < q3.x || y > q3.y);
+            tt[i * RTOW_LIST_TT_STRIDE] = t;
+            inb |= (in ? 1u : 0u) << i;
+            if (!(t < from || t > closest) && in) { any = true; closest = t; t1 = t; }
+        }
+        if (!any) return false;
+        from = (float)((double)t1 + 0.0001);
+        any = false; closest = FLT_MAX;
+#pragma unroll 1
+        for (int i = 0; i < cn; ++i) {
+            const float t = tt[i * RTOW_LIST_TT_STRIDE];
+            if (!(t < from || t > closest) && ((inb >> i) & 1u)) { any = true; closest = t; t2 = t; }
+        }
+        if (!any) return false;
+    } else
+#endif
 #pragma unroll 1
     for (int pass = 0; pass < 2; ++pass) {
         bool any = false;
@@ -442,7 +489,7 @@ static __device__ __noinline__ bool list_medium_t(const float4 *prog, int pid, c
     if (hitDistance < inside) { t_out = t1 + hitDistance / dlen; return true; }
     return false;
 }
-__device__ __forceinline__ bool list_hit(const float4 *prog, int n_top, const Ray &r, float tmin, float tmax, const Rng *g, float &t_out, int &prim_out) {
+__device__ __forceinline__ bool list_hit(const float4 *prog, int n_top, const Ray &r, float tmin, float tmax, const Rng *g, float *tt, float &t_out, int &prim_out) {
     bool any = false;
     float closest = tmax;
     int key = 0;
@@ -455,7 +502,7 @@ __device__ __forceinline__ bool list_hit(const float4 *prog, int n_top, const Ra
         float t;
         bool h;
         if (kind == RTOW_PRIM_MEDIUM) {
-            h = list_medium_t(prog, i, r, tmin, closest, g, t);
+            h = list_medium_t(prog, i, r, tmin, closest, g, tt, t);
         } else {
             const int k = __float_as_int(q0.y);
             if (k != key || k == RTOW_RAY_KEY_NONE) { list_xform(r, (__float_as_int(q0.x) >> 8) & 3, rec[1], rec[2], rr); key = k; }

@@ -7,39 +7,49 @@
 
 namespace rtow {
 
-// Perlin tables staged in shared memory by the render kernels (4 KB gradients + 768 B perms).
+// Perlin tables staged in shared memory by the render kernels (4 KB gradients + 1.5 KB perms).  The permutation entries are
+// staged as BYTE OFFSETS into the gradient table (value << 4, 16 bits each): XOR commutes with the shift, so the gradient of a
+// lattice corner sits at vec + (px ^ py ^ pz) -- one LOP3 and the load's own base + offset addressing, where byte tables cost a
+// mask and a scaled add per corner (16 integer instructions per octave, 112 per marble lookup).  Same table entries, same floats.
 struct PerlinSmem {
     float4 vec[256];
-    uint8_t perm[768];
+    uint16_t perm[768];
 };
 
 __device__ __forceinline__ void perlin_stage(const DScene &S, PerlinSmem *sm) {
     if (!S.has_perlin) return;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) sm->vec[i] = __ldg(&S.perlin_vec[i]);
-    for (int i = threadIdx.x; i < 768; i += blockDim.x) sm->perm[i] = __ldg(&S.perlin_perm[i]);
+    for (int i = threadIdx.x; i < 768; i += blockDim.x) sm->perm[i] = (uint16_t)((unsigned)__ldg(&S.perlin_perm[i]) << 4);
 }
 
 // noise.h:11-36 + mathUtilities.h:41-60.  The blend weights i*uu + (1-i)*(1-uu), i in {0,1},
 // are exactly uu or (1-uu); the product and sum order is the reference's.
+// -DRTOW_PERLIN_FMA contracts the corner dot products and the running sum (the noise value feeds a colour only, never a
+// decision, so paths and ray counts are unchanged; values move in the last bits).  Off by default: measured in DESIGN.md.
 __device__ __forceinline__ float perlin_noise(const PerlinSmem *pt, float px, float py, float pz) {
     float fx = floorf(px), fy = floorf(py), fz = floorf(pz);
     float u = px - fx, v = py - fy, w = pz - fz;
     int i = (int)fx, j = (int)fy, k = (int)fz;
     float uu = u * u * (3 - 2 * u), vv = v * v * (3 - 2 * v), ww = w * w * (3 - 2 * w);
     float accum = 0;
+    const char *vec = reinterpret_cast<const char *>(pt->vec);
 #pragma unroll
     for (int di = 0; di < 2; di++) {
-        int hx = pt->perm[(i + di) & 255];
+        unsigned hx = pt->perm[(i + di) & 255];
         float wu = di ? uu : 1 - uu;
 #pragma unroll
         for (int dj = 0; dj < 2; dj++) {
-            int hxy = hx ^ pt->perm[256 + ((j + dj) & 255)];
+            unsigned hxy = hx ^ pt->perm[256 + ((j + dj) & 255)];
             float wuv = wu * (dj ? vv : 1 - vv);
 #pragma unroll
             for (int dk = 0; dk < 2; dk++) {
-                float4 c = pt->vec[hxy ^ pt->perm[512 + ((k + dk) & 255)]];
+                float4 c = *reinterpret_cast<const float4 *>(vec + (hxy ^ pt->perm[512 + ((k + dk) & 255)]));
                 float wt = wuv * (dk ? ww : 1 - ww);
+#ifdef RTOW_PERLIN_FMA
+                accum = fmaf(wt, fmaf(c.z, w - dk, fmaf(c.y, v - dj, c.x * (u - di))), accum);
+#else
                 accum += wt * dot3(c.x, c.y, c.z, u - di, v - dj, w - dk);
+#endif
             }
         }
     }

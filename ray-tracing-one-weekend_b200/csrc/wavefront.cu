@@ -334,6 +334,8 @@ __global__ void __launch_bounds__(128, MINB) wf_extend_exact_kernel(DScene S, Wa
 // this one reads the scene's fixed-form records (rt_device.cuh list_hit) from shared memory.  Same arithmetic, same hits.
 __global__ void __launch_bounds__(128, 8) wf_extend_list_kernel(DScene S, WavefrontLaunch W, int parity) {
     __shared__ float4 s_prog[4 * RTOW_LIST_MAX];
+    __shared__ float s_tt[RTOW_LIST_BOX_MAX * RTOW_LIST_TT_STRIDE];      // per thread: the plane distances of a medium's boundary rectangles (list_medium_t)
+    static_assert(RTOW_LIST_TT_STRIDE == 128, "one scratch column per thread of the block");
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     for (int i = threadIdx.x; i < 4 * S.list_n; i += blockDim.x) s_prog[i] = __ldg(S.list_prog + i);
@@ -356,7 +358,7 @@ __global__ void __launch_bounds__(128, 8) wf_extend_list_kernel(DScene S, Wavefr
                 rng_init(g, W.L.seed, (uint32_t)id.x, (uint32_t)id.y);
                 g.bounce = (uint32_t)id.w;
                 float t = 0.f; int pid = -1;
-                if (!list_hit(s_prog, S.n_prims_top, r, 0.001f, FLT_MAX, &g, t, pid)) { t = 0.f; pid = -1; }
+                if (!list_hit(s_prog, S.n_prims_top, r, 0.001f, FLT_MAX, &g, s_tt + threadIdx.x, t, pid)) { t = 0.f; pid = -1; }
                 *reinterpret_cast<float2 *>(W.idh_in + 2 * slot + 1) = make_float2(t, __int_as_float(pid));
                 cls = pid >= 0 ? __ldg(&S.prim_class[pid]) : 0;
                 rays++;

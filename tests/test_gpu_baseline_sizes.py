@@ -1,6 +1,6 @@
 """-m gpu: parity at the sizes BASELINE.json quotes, through the C ABI.
 
-  * configs[4]: 1 M random spheres under the reference's BvhNode build, 2^20 coherent + 2^20 incoherent rays, both
+  * configs[4]: 1 M random spheres under the reference's BvhNode build, 2^20 coherent (far and near pinhole) + 2^20 incoherent rays, both
     traversals against the REFERENCE's own world->hit() (oracle/_ref; bvhNode.h:66-96, sphere.h:20-69): primitive id and
     material id exact, t / point / normal bit-identical (north_star asks for 1e-5 relative).
   * configs[1] and configs[3] frame sizes: one 1920x1080 and one 3840x2160 frame at 1 spp against the port oracle (same
@@ -21,7 +21,8 @@ def test_one_million_spheres_match_the_reference_on_2_20_rays_per_class(gpu, abi
     n_spheres, seed = 1000000, 12345
     host = gpu.HostScene("bvh_stress", seed=seed, n=n_spheres)
     dev = gpu.DeviceScene(host.desc)
-    sets = {"coherent": gpu.raysets.coherent_rays(1024), "incoherent": gpu.raysets.incoherent_rays(1 << 20, seed=7, extent=100.0)}
+    sets = {"coherent": gpu.raysets.coherent_rays(1024), "coherent_near": gpu.raysets.coherent_rays(1024, origin=(0.0, 0.0, -120.0)),
+            "incoherent": gpu.raysets.incoherent_rays(1 << 20, seed=7, extent=100.0)}
     if ob.have_ref():
         ref = ob.RefOracle()
         rs = ref.scene("bvh_stress", seed=seed, n=n_spheres)

@@ -38,6 +38,8 @@ def main():
     side = int(round(n ** 0.5))
     sets = {"coherent": pkg.raysets.coherent_rays(side) if args.scene == "bvh_stress" else pkg.raysets.camera_rays(pkg.main_camera(1920, 1080), 1920, 1080, n, seed=3),
             "incoherent": pkg.raysets.incoherent_rays(n, seed=7, extent=ext)}
+    if args.scene == "bvh_stress":
+        sets["coherent_near"] = pkg.raysets.coherent_rays(side, origin=(0.0, 0.0, -120.0))
     for name, rays in sets.items():
         d_rays = torch.from_numpy(rays.view(np.uint8).reshape(len(rays), -1).copy()).to(dev_t)
         d_hits = torch.empty(len(rays), 48, dtype=torch.uint8, device=dev_t)
