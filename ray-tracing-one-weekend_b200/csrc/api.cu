@@ -495,9 +495,10 @@ int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out)
                     const int t = desc->prims[c].type;
                     if ((t != RTOW_PRIM_RECT_XY && t != RTOW_PRIM_RECT_XZ && t != RTOW_PRIM_RECT_YZ) || ((uint32_t)dp[c].xform_count >> 8) != key0) run = false;
                 }
-                if (run && key0 != RTOW_RAY_KEY_NONE) {
+                const bool one_sphere = p.child_count == 1 && desc->prims[p.child_begin].type == RTOW_PRIM_SPHERE;
+                if ((run || one_sphere) && key0 != RTOW_RAY_KEY_NONE) {
                     int32_t w; std::memcpy(&w, &prog[4 * (size_t)i].x, 4);
-                    w |= RTOW_LIST_FLAG_BOX_RUN;
+                    w |= run ? RTOW_LIST_FLAG_BOX_RUN : RTOW_LIST_FLAG_SPHERE;
                     std::memcpy(&prog[4 * (size_t)i].x, &w, 4);
                 }
             }

@@ -386,6 +386,7 @@ __device__ __noinline__ bool object_hit(const DScene &S, const Ray r, float tmin
 #define RTOW_LIST_FORM_T 1
 #define RTOW_LIST_FORM_R 2
 #define RTOW_LIST_FLAG_BOX_RUN (1 << 10)   // medium record: the boundary is <= RTOW_LIST_BOX_MAX rectangles behind one wrapper chain (api.cu)
+#define RTOW_LIST_FLAG_SPHERE (1 << 11)    // medium record: the boundary is one Sphere
 #define RTOW_LIST_BOX_MAX 8
 #define RTOW_LIST_TT_STRIDE 128             // threads per block of wf_extend_list_kernel: one scratch column per thread
 __device__ __forceinline__ void list_xform(const Ray &r_in, int form, const float4 &q1, const float4 &q2, Ray &r) {
@@ -460,6 +461,31 @@ static __device__ __noinline__ bool list_medium_t(const float4 *prog, int pid, c
             if (!(t < from || t > closest) && ((inb >> i) & 1u)) { any = true; closest = t; t2 = t; }
         }
         if (!any) return false;
+    } else if (__float_as_int(q0.x) & RTOW_LIST_FLAG_SPHERE) {
+        // The boundary is one Sphere: both queries solve the same quadratic (sphere.h:26-42), so it is set up once and the
+        // two roots are offered to the two intervals in sphere_t's order (near root first, then the far one).
+        const float4 *c = prog + 4 * cb;
+        {
+            const float4 c0 = c[0];
+            const int ck = __float_as_int(c0.y);
+            if (ck != key) list_xform(r, (__float_as_int(c0.x) >> 8) & 3, c[1], c[2], rr);
+        }
+        const float4 q2 = c[2], q3 = c[3];
+        const float ocx = rr.ox - q2.z, ocy = rr.oy - q2.w, ocz = rr.oz - q3.x;
+        const float a = dot3(rr.dx, rr.dy, rr.dz, rr.dx, rr.dy, rr.dz);
+        const float b = dot3(rr.dx, rr.dy, rr.dz, ocx, ocy, ocz);
+        const float cc = dot3(ocx, ocy, ocz, ocx, ocy, ocz) - q3.y * q3.y;
+        const float disc = b * b - a * cc;
+        if (!(disc > 0)) return false;
+        const float sq = sqrtf(disc);
+        const float r1 = (-b - sq) / a, r2 = (-b + sq) / a;
+        if (r1 < FLT_MAX && r1 > from) t1 = r1;
+        else if (r2 < FLT_MAX && r2 > from) t1 = r2;
+        else return false;
+        from = (float)((double)t1 + 0.0001);
+        if (r1 < FLT_MAX && r1 > from) t2 = r1;
+        else if (r2 < FLT_MAX && r2 > from) t2 = r2;
+        else return false;
     } else
 #endif
 #pragma unroll 1
