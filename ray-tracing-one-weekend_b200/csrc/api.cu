@@ -486,7 +486,9 @@ int rtow_scene_create(const rtow_scene_desc *desc, int device, rtow_scene **out)
             // A medium whose boundary is a run of at most RTOW_LIST_BOX_MAX rectangles behind ONE wrapper chain (a Box, the case of
             // every reference scene): flagged so that list_medium_t keeps the rectangles' plane distances of its first boundary
             // query for the second one (constantMedium.h:32,36 ask the same boundary twice with different intervals).
-            for (int i = 0; i < desc->n_prims && ok; ++i) {
+            const char *once_env = getenv("RTOW_LIST_BOUNDARY_ONCE");        // 0: no flags, every medium takes the generic two-pass walk (A/B, tests)
+            const bool boundary_once = !once_env || atoi(once_env) != 0;
+            for (int i = 0; i < desc->n_prims && ok && boundary_once; ++i) {
                 const rtow_prim &p = desc->prims[i];
                 if (p.type != RTOW_PRIM_MEDIUM || p.child_count < 1 || p.child_count > RTOW_LIST_BOX_MAX) continue;
                 bool run = true;
@@ -732,9 +734,15 @@ int rtow_render_accumulate_moments_device(rtow_scene *s, const rtow_camera *cam,
         // the per-launch tails better: measured on B200 at 1024 spp of the configs[1] scene 2^20 / 2^21 / 2^22 / 2^23 / 2^24 / 2^25
         // entries = 2762 / 3033 / 3179 / 3288 / 3333 / 3338 Mpaths/s, and at the 128 spp an 8-GPU shard renders 3003 (2^21) / 3228 /
         // 3223 / 3155; Cornell + smoke 737 / 752 / 766 / 768 / 766 / 753.  Default 2^23 = 1 GB of state + 0.5 GB of queues.
-        static const long long pool_cap = [] { const char *e = getenv("RTOW_WF_POOL"); return e ? atoll(e) : (1ll << 23); }();
+        // End of round 2, final kernels, 1024 spp: 2^23 / 2^24 / 2^25 = 3368 / 3416 / 3427.  So the default follows the size of the job:
+        // the longest stream of 2^23 .. 2^25 entries that still leaves 32 stream-fulls of work items (an 8-GPU shard of 128 spp
+        // keeps 2^23, the 512-spp frame of configs[2] takes 2^24, the 1024-spp frame of configs[1] 2^25 = 4 GB of state + 2 GB of
+        // queues, held by the scene until it is destroyed; RTOW_WF_POOL pins the length).
+        static const long long pool_env = [] { const char *e = getenv("RTOW_WF_POOL"); return e ? atoll(e) : 0ll; }();
         const long long n_pixels = (long long)L.pixel_count;
         const unsigned long long items = (unsigned long long)((n_pixels + 31) / 32) * 32ull * (unsigned)L.sample_count;
+        long long pool_cap = pool_env > 0 ? pool_env : (1ll << 23);
+        if (pool_env <= 0) while (pool_cap < (1ll << 25) && items >= 64ull * (unsigned long long)pool_cap) pool_cap <<= 1;
         long long pool = (long long)std::min<unsigned long long>(items, (unsigned long long)pool_cap);
         pool = (pool + 255) / 256 * 256;
         if (int rc = ensure_wavefront(s, (int)pool, (size_t)n_pixels)) return rc;

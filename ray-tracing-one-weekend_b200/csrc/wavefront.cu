@@ -601,12 +601,13 @@ cudaError_t run_wavefront(const DScene &S, const rtow_camera &cam, WavefrontLaun
                           cudaStream_t stream, uint32_t *launches_out, WavefrontProfile *prof) {
     // Lane refill pays when traversals are long (a million spheres: ~55 node visits per ray); on a scene of a few dozen
     // nodes a ray takes ~3 steps and the refill's load latency would dominate, so a warp then runs (almost) whole batches of 32.
-    // (round 2, dense stream: on the small scene a refill below 8 live lanes, leaves only when no lane waits at a node, and
+    // (round 2, dense stream: on the small scene a refill below 8 live lanes -- later 2 --, leaves only when no lane waits at a node, and
     // 8 blocks x 64 registers measured 3335 against 3264 Mpaths/s with round 1's 1 / 8 / 5; on a million spheres the leaf rule
     // alone costs 2x, so the big-tree defaults stay)
     const bool small_tree = S.fast_n_nodes < 4096;
     static const int refill_env = [] { const char *e = getenv("RTOW_WF_REFILL"); return e ? atoi(e) : -1; }();
-    const int refill = refill_env >= 0 ? refill_env : (small_tree ? 8 : 28);
+    // (end of round 2, the same scene at 256 spp: refill below 2 / 4 / 6 / 8 live lanes = 3367 / 3360 / 3353 / 3342 Mpaths/s, twice each)
+    const int refill = refill_env >= 0 ? refill_env : (small_tree ? 2 : 28);
     static const int leaf_env = [] { const char *e = getenv("RTOW_TRACE_LEAFMIN"); return e ? atoi(e) : -1; }();
     const int leaf_min = leaf_env >= 0 ? leaf_env : (small_tree ? 32 : 8);
     static const int static_env = [] { const char *e = getenv("RTOW_WF_STATIC_CLAIM"); return e ? atoi(e) : 0; }();

@@ -121,6 +121,27 @@ def test_wavefront_fallback_to_the_reference_walk(gpu, abi, tmp_path):
     assert outs[0][0].tobytes() == outs[1][0].tobytes()   # same image, bit for bit
 
 
+@pytest.mark.parametrize("name", ["cornell_smoke_ned", "cornell_ned"])
+def test_medium_boundary_evaluated_once_equals_the_two_pass_walk(gpu, abi, monkeypatch, name):
+    """wf_extend_list_kernel evaluates a medium's boundary once for both queries of constantMedium.h:32,36 when it is a Box
+    (a run of rectangles behind one chain) or one Sphere.  RTOW_LIST_BOUNDARY_ONCE=0 (read when the scene is uploaded) leaves
+    the records unflagged, so every medium takes the generic two-pass walk: same image bit for bit, same ray counts."""
+    host = gpu.HostScene(name, seed=12345, wrap=True)
+    W, H = 128, 72
+    cam = gpu.main_camera(W, H)
+    p = abi.default_render_params(W, H, 24, seed=11, kernel=abi.KERNEL_WAVEFRONT)
+    outs = []
+    for knob in ("1", "0"):
+        monkeypatch.setenv("RTOW_LIST_BOUNDARY_ONCE", knob)
+        dev = gpu.DeviceScene(host.desc)
+        img, st = dev.render(cam, p)
+        outs.append((img.copy(), st.rays, st.paths))
+        dev.close()
+    assert outs[0][1:] == outs[1][1:]
+    assert outs[0][0].tobytes() == outs[1][0].tobytes()
+    assert outs[0][1] > 4 * W * H * 24            # long paths: the media and the boxes were walked
+
+
 def test_render_is_deterministic_and_shard_invariant(gpu, abi):
     """spp sharding: the union of the shards' samples is the full image's sample set."""
     import torch
