@@ -267,7 +267,11 @@ int rtow_render(rtow_scene *scene, const rtow_camera *cam, const rtow_render_par
 /* Adds the radiance SUM of samples [sample_begin, +sample_count) into d_accum (W*H*3 floats
  * on the scene's device, row 0 = top).  All work is issued on `stream`; the megakernel path returns without
  * waiting, the wavefront path polls the path pool for completion and so synchronises `stream` before returning.
- * Counters are read with rtow_stream_stats. */
+ * Counters are read with rtow_stream_stats.
+ * Device memory: the wavefront path keeps its path stream with the scene (allocated at the first call that needs it,
+ * grown when a later call needs more, freed by rtow_scene_destroy): 192 bytes per entry, 2^23 .. 2^25 entries chosen by
+ * the size of the job -- 1.5 GB for frames up to 1080p x 256 spp, 6 GB from 1080p x 1024 spp on -- or as many entries
+ * as the environment variable RTOW_WF_POOL says; plus 24 bytes per pixel. */
 int rtow_render_accumulate_device(rtow_scene *scene, const rtow_camera *cam,
                                   const rtow_render_params *params, float *d_accum, void *stream);
 
