@@ -223,9 +223,6 @@ __device__ __forceinline__ void fast_node(const DScene &S, FastTrav &T, STACK &s
     const float aix = fabsf(T.ix), aiy = fabsf(T.iy), aiz = fabsf(T.iz);
     const float ub = T.bestc * 1.000001f;
     const float inf = __int_as_float(0x7f800000);
-#ifdef RTOW_FAST_AMAX
-    const float amax = fmaxf(fmaxf(aix, aiy), aiz);
-#endif
     float d[4]; int ref[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -235,19 +232,10 @@ __device__ __forceinline__ void fast_node(const DScene &S, FastTrav &T, STACK &s
         // exit distance under the ray's current slack bounds every accepted t in this child -> the child's own slack
         // (no min with ub: T.eta already is <= Kd * bestc + base; no max with 0: a child whose exit lies behind the
         // ray holds no hit and whatever slack it gets can only make it cull or cost a wasted visit)
-#ifdef RTOW_FAST_AMAX
-        // experiment: one slack term in t for all three axes (the largest |1/d_i|): looser boxes, 8 instructions less per child
-        const float nr = fmaxf(fmaxf(nxk, nyk), nzk), fr = fminf(fminf(fxk, fyk), fzk);
-        const float tf0 = fmaf(T.eta, amax, fr);
-        const float ek = fminf(T.eta, fmaf(T.Kd, tf0 * 1.000001f, T.base));
-        const float tn = fmaxf(fmaf(-ek, amax, nr), T.tmin);
-        const float tf = fminf(fmaf(ek, amax, fr), ub);
-#else
         const float tf0 = fminf(fminf(fmaf(T.eta, aix, fxk), fmaf(T.eta, aiy, fyk)), fmaf(T.eta, aiz, fzk));
         const float ek = fminf(T.eta, fmaf(T.Kd, tf0 * 1.000001f, T.base));
         const float tn = fmaxf(fmaxf(fmaf(-ek, aix, nxk), fmaf(-ek, aiy, nyk)), fmaxf(fmaf(-ek, aiz, nzk), T.tmin));
         const float tf = fminf(fminf(fmaf(ek, aix, fxk), fmaf(ek, aiy, fyk)), fminf(fmaf(ek, aiz, fzk), ub));
-#endif
         ref[k] = __float_as_int(lane4(q3, k));
         d[k] = tn <= tf ? tn : inf;      // unused slots: inverted byte interval, and their ref is a never-hit leaf
     }
