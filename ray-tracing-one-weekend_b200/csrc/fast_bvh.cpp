@@ -4,9 +4,12 @@
 #include "fast_bvh.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <thread>
 
 namespace rtow {
 namespace {
@@ -89,11 +92,40 @@ struct BNode {
     int obj = -1;                // >= 0: leaf
 };
 
+// Runs f(i) for i in [0, n) on up to `threads` host threads (indices are claimed from a counter; f must not care who runs it).
+template <class F>
+void parallel_for(int n, int threads, const F &f) {
+    threads = std::max(1, std::min(threads, n));
+    if (threads == 1) { for (int i = 0; i < n; ++i) f(i); return; }
+    std::atomic<int> next(0);
+    std::vector<std::thread> pool;
+    auto work = [&] { for (int i = next++; i < n; i = next++) f(i); };
+    for (int t = 1; t < threads; ++t) pool.emplace_back(work);
+    work();
+    for (auto &t : pool) t.join();
+}
+int host_threads() {
+    static const int n = [] {
+        const char *e = getenv("RTOW_BVH_THREADS");
+        if (e && atoi(e) > 0) return atoi(e);
+        const unsigned hc = std::thread::hardware_concurrency();
+        return (int)std::max(1u, std::min(hc ? hc : 1u, 32u));
+    }();
+    return n;
+}
+
 struct Builder {
     const std::vector<DBox> &boxes;
     std::vector<double> cx, cy, cz;
     std::vector<int> idx;
     std::vector<BNode> nodes;
+    // Subtrees of at most `cutoff` objects are built as independent tasks on the host's threads (the top of the tree, whose
+    // splits sweep the whole object array, is built first).  A subtree over m objects has exactly 2m - 1 nodes, so every
+    // task writes its nodes straight into its own block of the one node array.  The split of the work depends on the
+    // object count alone, so the tree -- and its node numbering -- is the same on every machine and every run.
+    struct Task { int b, e, parent, side, base; };
+    std::vector<Task> tasks;
+    int cutoff = 0;
 
     explicit Builder(const std::vector<DBox> &b) : boxes(b) {
         size_t n = b.size();
@@ -105,31 +137,91 @@ struct Builder {
     }
     double cen(int o, int a) const { return a == 0 ? cx[o] : a == 1 ? cy[o] : cz[o]; }
 
-    int build(int b, int e) {
-        int me = (int)nodes.size();
-        nodes.emplace_back();
-        DBox bb, cb;
-        for (int i = b; i < e; ++i) {
-            bb.grow(boxes[idx[i]]);
-            double c[3] = {cx[idx[i]], cy[idx[i]], cz[idx[i]]};
-            cb.grow(c);
+    int build_all() {
+        const int n = (int)boxes.size();
+        nodes.assign((size_t)2 * n - 1, BNode());
+        int cursor = 0;
+        if (n < (1 << 15)) return build(0, n, cursor, -1, 0);
+        cutoff = std::max(1 << 12, n >> 7);
+        std::vector<BNode> all;
+        all.swap(nodes);                       // the top of the tree goes to a small array of its own first
+        nodes.assign(4 * (size_t)(n / cutoff + 1) + 8, BNode());
+        const int root = build(0, n, cursor, -1, 0);
+        const int n_top = cursor;
+        std::vector<BNode> top;
+        top.swap(nodes);
+        nodes.swap(all);
+        int next = n_top;
+        for (Task &k : tasks) { k.base = next; next += 2 * (k.e - k.b) - 1; }
+        for (int i = 0; i < n_top; ++i) nodes[i] = top[i];
+        for (const Task &k : tasks) (k.side ? nodes[k.parent].right : nodes[k.parent].left) = k.base;
+        parallel_for((int)tasks.size(), host_threads(), [&](int t) {
+            int cur = tasks[t].base;
+            build(tasks[t].b, tasks[t].e, cur, -2, 0);
+        });
+        return root;
+    }
+
+    // parent >= 0 (or -1 for the root): building the shared top of the tree, ranges of <= cutoff objects become tasks;
+    // parent == -2: inside a task (no further tasks)
+    int build(int b, int e, int &cursor, int parent, int side) {
+        std::vector<BNode> &out = nodes;
+        if (parent != -2 && cutoff > 0 && parent >= 0 && e - b <= cutoff) {
+            tasks.push_back(Task{b, e, parent, side, -1});
+            return -1;      // patched when the task's nodes are appended
         }
-        nodes[me].box = bb;
-        if (e - b == 1) { nodes[me].obj = idx[b]; return me; }
+        const int me = cursor++;
+        // the two sweeps over the range (bounds, then bins) are reductions of exact min / max / counts: on the big ranges of
+        // the serial top phase they run in slices on the host's threads and give the same numbers
+        const int T = (parent != -2 && cutoff > 0 && e - b > cutoff) ? host_threads() : 1;
+        auto slice = [&](int t, int &lo, int &hi) { lo = b + (int)((long long)(e - b) * t / T); hi = b + (int)((long long)(e - b) * (t + 1) / T); };
+        DBox bb, cb;
+        {
+            std::vector<DBox> pb(T), pc(T);
+            parallel_for(T, T, [&](int t) {
+                int lo, hi; slice(t, lo, hi);
+                DBox x, y;
+                for (int i = lo; i < hi; ++i) {
+                    x.grow(boxes[idx[i]]);
+                    double c[3] = {cx[idx[i]], cy[idx[i]], cz[idx[i]]};
+                    y.grow(c);
+                }
+                pb[t] = x; pc[t] = y;
+            });
+            for (int t = 0; t < T; ++t) { if (pb[t].valid()) bb.grow(pb[t]); if (pc[t].valid()) cb.grow(pc[t]); }
+        }
+        out[me].box = bb;
+        if (e - b == 1) { out[me].obj = idx[b]; return me; }
         const int NB = 16;
+        struct Bins { DBox box[3][NB]; int n[3][NB]; };
+        bool use[3]; double blo[3], bscale[3];
+        for (int a = 0; a < 3; ++a) {
+            const double ext = cb.hi[a] - cb.lo[a];
+            use[a] = ext > 0; blo[a] = cb.lo[a]; bscale[a] = use[a] ? NB / ext : 0.0;
+        }
+        std::vector<Bins> part(T);
+        parallel_for(T, T, [&](int t) {
+            int lo, hi; slice(t, lo, hi);
+            Bins &S = part[t];
+            for (int a = 0; a < 3; ++a) for (int k = 0; k < NB; ++k) S.n[a][k] = 0;
+            for (int i = lo; i < hi; ++i) {
+                const int o = idx[i];
+                for (int a = 0; a < 3; ++a) {
+                    if (!use[a]) continue;
+                    int k = (int)((cen(o, a) - blo[a]) * bscale[a]);
+                    k = k < 0 ? 0 : k >= NB ? NB - 1 : k;
+                    S.n[a][k]++; S.box[a][k].grow(boxes[o]);
+                }
+            }
+        });
+        Bins &B0 = part[0];
+        for (int t = 1; t < T; ++t)
+            for (int a = 0; a < 3; ++a) for (int k = 0; k < NB; ++k) if (part[t].n[a][k]) { B0.n[a][k] += part[t].n[a][k]; B0.box[a][k].grow(part[t].box[a][k]); }
         int best_axis = -1, best_bin = -1;
         double best_cost = 1e300;
         for (int a = 0; a < 3; ++a) {
-            double lo = cb.lo[a], ext = cb.hi[a] - cb.lo[a];
-            if (!(ext > 0)) continue;
-            DBox bin_box[NB]; int bin_n[NB];
-            for (int k = 0; k < NB; ++k) bin_n[k] = 0;
-            double scale = NB / ext;
-            for (int i = b; i < e; ++i) {
-                int k = (int)((cen(idx[i], a) - lo) * scale);
-                k = k < 0 ? 0 : k >= NB ? NB - 1 : k;
-                bin_n[k]++; bin_box[k].grow(boxes[idx[i]]);
-            }
+            if (!use[a]) continue;
+            const DBox *bin_box = B0.box[a]; const int *bin_n = B0.n[a];
             double right_area[NB]; int right_n[NB];
             DBox acc; int cnt = 0;
             for (int k = NB - 1; k > 0; --k) {
@@ -160,9 +252,10 @@ struct Builder {
             mid = (int)(it - idx.begin());
             if (mid == b || mid == e) mid = (b + e) / 2;
         }
-        int l = build(b, mid);
-        int r = build(mid, e);
-        nodes[me].left = l; nodes[me].right = r;
+        const int next_parent = parent == -2 ? -2 : me;
+        int l = build(b, mid, cursor, next_parent, 0);
+        int r = build(mid, e, cursor, next_parent, 1);
+        out[me].left = l; out[me].right = r;
         return me;
     }
 };
@@ -244,8 +337,7 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
     }
 
     Builder B(boxes);
-    B.nodes.reserve((size_t)2 * n);
-    int broot = B.build(0, n);
+    int broot = B.build_all();
 
     // collapse to 4-wide, depth first, into wide nodes with float boxes; they are quantised afterwards
     const double pad_rel = 4e-7;
@@ -311,7 +403,10 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
     // placed at least cell/64 outside the float box (lo down, hi up): the decoded box contains the float box with
     // that margin and culling stays conservative.
     out.nodes.assign(wide.size() * FAST_NODE_F4, make_float4(0, 0, 0, 0));
-    for (size_t id = 0; id < wide.size(); ++id) {
+    std::atomic<bool> too_large(false);
+    const int n_chunks = (int)((wide.size() + 4095) / 4096);       // nodes are independent: chunks of 4096 on the host's threads
+    parallel_for(n_chunks, wide.size() >= (1u << 15) ? host_threads() : 1, [&](int chunk) {
+    for (size_t id = (size_t)chunk * 4096; id < std::min(wide.size(), (size_t)(chunk + 1) * 4096); ++id) {
         const Wide &w = wide[id];
         float p[3]; uint32_t ebyte[3]; uint32_t qlo[3] = {0, 0, 0}, qhi[3] = {0, 0, 0};
         for (int a = 0; a < 3; ++a) {
@@ -326,7 +421,7 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
             }
             uint32_t lq[4], hq[4];
             for (;; ++e) {     // raise e until every plane, with its margin, fits in a byte
-                if (e > 100) return fail("box extent too large to quantise");
+                if (e > 100) { too_large = true; return; }
                 const double cell = std::ldexp(1.0, e), margin = cell / 64.0;
                 const float pf = (float)((double)mn - cell / 32.0 - 32768.0 * cell);
                 const double origin = (double)pf + 32768.0 * cell;      // where byte 0 decodes to
@@ -357,6 +452,8 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
         for (int k = 0; k < 4; ++k) ref[k] = w.ref[k] == FAST_EMPTY ? ~(int32_t)(FAST_LEAF_SPHERE | n) : w.ref[k];
         nd[3] = make_float4(i2f(ref[0]), i2f(ref[1]), i2f(ref[2]), i2f(ref[3]));
     }
+    });
+    if (too_large) return fail("box extent too large to quantise");
     return true;
 }
 

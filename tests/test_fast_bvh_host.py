@@ -26,3 +26,18 @@ def test_decoded_nodes_contain_their_content(checker, scene, n):
     assert out.returncode == 0 and out.stdout.startswith("ok"), out.stdout + out.stderr
     nodes, leaves = map(int, out.stdout.split()[1:3])
     assert leaves >= max(n, 1) and nodes >= 1
+
+
+def test_the_threaded_build_gives_the_same_structure_for_any_thread_count(checker):
+    """build_fast_bvh builds subtrees of a big scene on the host's threads (csrc/fast_bvh.cpp); how the work is cut depends on
+    the object count alone, so the node array is the same byte for byte with 1, 3 or all threads."""
+    hashes = set()
+    for threads in ("1", "3", ""):
+        env = dict(os.environ)
+        env.pop("RTOW_BVH_THREADS", None)
+        if threads:
+            env["RTOW_BVH_THREADS"] = threads
+        out = subprocess.run([checker, "bvh_stress", "70000"], capture_output=True, text=True, cwd=ROOT, env=env)
+        assert out.returncode == 0 and out.stdout.startswith("ok"), out.stdout + out.stderr
+        hashes.add(out.stdout.split()[3])
+    assert len(hashes) == 1
