@@ -734,15 +734,12 @@ int rtow_render_accumulate_moments_device(rtow_scene *s, const rtow_camera *cam,
         // the per-launch tails better: measured on B200 at 1024 spp of the configs[1] scene 2^20 / 2^21 / 2^22 / 2^23 / 2^24 / 2^25
         // entries = 2762 / 3033 / 3179 / 3288 / 3333 / 3338 Mpaths/s, and at the 128 spp an 8-GPU shard renders 3003 (2^21) / 3228 /
         // 3223 / 3155; Cornell + smoke 737 / 752 / 766 / 768 / 766 / 753.  Default 2^23 = 1 GB of state + 0.5 GB of queues.
-        // End of round 2, final kernels, 1024 spp: 2^23 / 2^24 / 2^25 = 3368 / 3416 / 3427.  So the default follows the size of the job:
-        // the longest stream of 2^23 .. 2^25 entries that still leaves 32 stream-fulls of work items (an 8-GPU shard of 128 spp
-        // keeps 2^23, the 512-spp frame of configs[2] takes 2^24, the 1024-spp frame of configs[1] 2^25 = 4 GB of state + 2 GB of
-        // queues, held by the scene until it is destroyed; RTOW_WF_POOL pins the length).
-        static const long long pool_env = [] { const char *e = getenv("RTOW_WF_POOL"); return e ? atoll(e) : 0ll; }();
+        // End of round 2, final kernels, 1024 spp on one GPU: 2^23 / 2^24 / 2^25 = 3368 / 3416 / 3427 Mpaths/s (+1.4 / +1.8 %, for 3 / 6 GB
+        // of scratch instead of 1.5), nothing at the 128 spp of an 8-GPU shard.  The default stays 2^23; RTOW_WF_POOL=<entries> is
+        // the knob for long single-GPU jobs.
+        static const long long pool_cap = [] { const char *e = getenv("RTOW_WF_POOL"); return e && atoll(e) > 0 ? atoll(e) : (1ll << 23); }();
         const long long n_pixels = (long long)L.pixel_count;
         const unsigned long long items = (unsigned long long)((n_pixels + 31) / 32) * 32ull * (unsigned)L.sample_count;
-        long long pool_cap = pool_env > 0 ? pool_env : (1ll << 23);
-        if (pool_env <= 0) while (pool_cap < (1ll << 25) && items >= 64ull * (unsigned long long)pool_cap) pool_cap <<= 1;
         long long pool = (long long)std::min<unsigned long long>(items, (unsigned long long)pool_cap);
         pool = (pool + 255) / 256 * 256;
         if (int rc = ensure_wavefront(s, (int)pool, (size_t)n_pixels)) return rc;
