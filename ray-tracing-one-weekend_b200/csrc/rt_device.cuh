@@ -420,7 +420,6 @@ static __device__ __noinline__ bool list_medium_t(const float4 *prog, int pid, c
     int key = 0;
     Ray rr = r;
     float from = -FLT_MAX;
-#ifndef RTOW_NO_LIST_BOX_RUN
     if (__float_as_int(q0.x) & RTOW_LIST_FLAG_BOX_RUN) {
         // The boundary is a run of rectangles behind one wrapper chain (a Box).  constantMedium.h:32 and :36 ask it twice, with
         // (-FLT_MAX, FLT_MAX) and (t1 + 0.0001, FLT_MAX); a rectangle's plane distance t = (k - o) / d and its in-bounds test
@@ -487,7 +486,6 @@ static __device__ __noinline__ bool list_medium_t(const float4 *prog, int pid, c
         else if (r2 < FLT_MAX && r2 > from) t2 = r2;
         else return false;
     } else
-#endif
 #pragma unroll 1
     for (int pass = 0; pass < 2; ++pass) {
         bool any = false;
