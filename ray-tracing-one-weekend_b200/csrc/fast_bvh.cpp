@@ -171,6 +171,9 @@ struct Builder {
             return -1;      // patched when the task's nodes are appended
         }
         const int me = cursor++;
+        // (the top of the tree is built into an array sized for balanced splits; a scene whose splits peel a few objects off
+        // per level needs more -- only this serial phase may grow it: a task's block is exactly 2m - 1 nodes)
+        if (parent != -2 && (size_t)me >= out.size()) out.resize(std::max(out.size() * 2, (size_t)me + 1));
         // the two sweeps over the range (bounds, then bins) are reductions of exact min / max / counts: on the big ranges of
         // the serial top phase they run in slices on the host's threads and give the same numbers
         const int T = (parent != -2 && cutoff > 0 && e - b > cutoff) ? host_threads() : 1;
