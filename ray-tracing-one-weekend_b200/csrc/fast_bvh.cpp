@@ -90,6 +90,7 @@ struct BNode {
     DBox box;
     int left = -1, right = -1;   // binary node indices
     int obj = -1;                // >= 0: leaf
+    int cnt = 0;                 // objects below
 };
 
 // Runs f(i) for i in [0, n) on up to `threads` host threads (indices are claimed from a counter; f must not care who runs it).
@@ -194,6 +195,7 @@ struct Builder {
             for (int t = 0; t < T; ++t) { if (pb[t].valid()) bb.grow(pb[t]); if (pc[t].valid()) cb.grow(pc[t]); }
         }
         out[me].box = bb;
+        out[me].cnt = e - b;
         if (e - b == 1) { out[me].obj = idx[b]; return me; }
         const int NB = 16;
         struct Bins { DBox box[3][NB]; int n[3][NB]; };
@@ -342,33 +344,23 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
     Builder B(boxes);
     int broot = B.build_all();
 
-    // collapse to 4-wide, depth first, into wide nodes with float boxes; they are quantised afterwards
+    // collapse to 4-wide, depth first, into wide nodes with float boxes; they are quantised afterwards.
+    // A wide node takes its id when it is popped from the stack, so ids are the pre-order of the wide tree with the children
+    // taken last slot first, and a subtree occupies one contiguous run of ids.  On big scenes that is used to collapse the
+    // subtrees below a frontier on the host's threads: the top is walked serially and only records, in pop order, its own
+    // nodes and the frontier subtrees; each of those is collapsed into a block of its own with ids from 0; the run of a
+    // block starts at the number of nodes popped before it.  Same ids, same node array as the one-thread walk.
     const double pad_rel = 4e-7;
     struct Wide { float lo[3][4], hi[3][4]; int32_t ref[4]; int nk; };
-    std::vector<Wide> wide;
-    wide.reserve((size_t)n / 2 + 1);
     struct Item { int bnode; int slot_node; int slot; int depth; };
-    std::vector<Item> stack;
-    auto new_node = [&]() {
+    auto empty_node = [] {
         Wide w;
         std::memset(&w, 0, sizeof w);
         for (int k = 0; k < 4; ++k) w.ref[k] = FAST_EMPTY;
-        wide.push_back(w);
-        return (int)wide.size() - 1;
+        return w;
     };
-    out.root = new_node();
-    stack.push_back({broot, -1, -1, 1});
-    out.max_depth = 1;
-    bool first = true;
-    while (!stack.empty()) {
-        Item it = stack.back(); stack.pop_back();
-        out.max_depth = std::max(out.max_depth, it.depth);
-        int id;
-        if (first) { id = out.root; first = false; }
-        else {
-            id = new_node();
-            wide[it.slot_node].ref[it.slot] = id;
-        }
+    // fills wide node `w` (id `id` in its array) from binary node it.bnode; internal children go to `stack` in slot order
+    auto expand = [&](const Item &it, int id, Wide &w, std::vector<Item> &stack) {
         int kids[4]; int nk = 0;
         const BNode &bn = B.nodes[it.bnode];
         if (bn.obj >= 0) { kids[nk++] = it.bnode; }
@@ -386,17 +378,99 @@ bool build_fast_bvh(const rtow_scene_desc *d, FastBvh &out, std::string *why) {
                 kids[nk++] = B.nodes[c].right;
             }
         }
-        wide[id].nk = nk;
+        w.nk = nk;
         for (int k = 0; k < nk; ++k) {
             const BNode &c = B.nodes[kids[k]];
             for (int a = 0; a < 3; ++a) {
                 double pad = pad_rel * (ext + std::fabs(c.box.lo[a]) + std::fabs(c.box.hi[a])) + 1e-30;
-                wide[id].lo[a][k] = down(c.box.lo[a], pad);
-                wide[id].hi[a][k] = up(c.box.hi[a], pad);
+                w.lo[a][k] = down(c.box.lo[a], pad);
+                w.hi[a][k] = up(c.box.hi[a], pad);
             }
-            if (c.obj >= 0) wide[id].ref[k] = leaf_ref[c.obj];
+            if (c.obj >= 0) w.ref[k] = leaf_ref[c.obj];
             else stack.push_back({kids[k], id, k, it.depth + 1});
         }
+    };
+    // the whole subtree of `root_item` into `W` (ids = positions in W, the root at W.size() on entry); returns the deepest level
+    auto collapse = [&](const Item &root_item, std::vector<Wide> &W) {
+        std::vector<Item> stack{root_item};
+        int deepest = root_item.depth;
+        bool first = true;
+        while (!stack.empty()) {
+            Item it = stack.back(); stack.pop_back();
+            deepest = std::max(deepest, it.depth);
+            const int id = (int)W.size();
+            W.push_back(empty_node());
+            if (!first) W[it.slot_node].ref[it.slot] = id;
+            first = false;
+            Wide w = W[id];
+            expand(it, id, w, stack);
+            W[id] = w;
+        }
+        return deepest;
+    };
+    std::vector<Wide> wide;
+    out.root = 0;
+    out.max_depth = 1;
+    const int frontier = n >= (1 << 15) ? std::max(1 << 10, n >> 8) : 0;      // objects below a frontier subtree; 0: one thread
+    if (!frontier) {
+        wide.reserve((size_t)n / 2 + 1);
+        out.max_depth = collapse({broot, -1, -1, 1}, wide);
+    } else {
+        struct Sub { Item it; std::vector<Wide> W; int deepest = 0; int base = 0; };
+        struct Event { int top; int sub; };                    // pop order: a node of the top (index into `top`) or a frontier subtree
+        std::vector<Wide> top;                                 // ids local to the top: refs between top nodes are patched below
+        std::vector<Item> top_item;
+        std::vector<Sub> subs;
+        std::vector<Event> events;
+        std::vector<Item> stack{{broot, -1, -1, 1}};
+        while (!stack.empty()) {
+            Item it = stack.back(); stack.pop_back();
+            if (it.slot_node >= 0 && B.nodes[it.bnode].cnt <= frontier) {
+                events.push_back({-1, (int)subs.size()});
+                subs.emplace_back();
+                subs.back().it = it;
+                continue;
+            }
+            out.max_depth = std::max(out.max_depth, it.depth);
+            const int id = (int)top.size();
+            events.push_back({id, -1});
+            top.push_back(empty_node());
+            top_item.push_back(it);
+            Wide w = top[id];
+            expand(it, id, w, stack);
+            top[id] = w;
+        }
+        parallel_for((int)subs.size(), host_threads(), [&](int i) {
+            Sub &sb = subs[i];
+            sb.W.reserve((size_t)B.nodes[sb.it.bnode].cnt / 2 + 1);
+            Item root_item = sb.it;
+            root_item.slot_node = -1;
+            sb.deepest = collapse(root_item, sb.W);
+        });
+        std::vector<int> top_id(top.size());
+        size_t total = 0;
+        for (const Event &e : events) {
+            if (e.top >= 0) top_id[e.top] = (int)total++;
+            else { subs[e.sub].base = (int)total; total += subs[e.sub].W.size(); }
+        }
+        wide.assign(total, empty_node());
+        for (size_t t = 0; t < top.size(); ++t) {
+            wide[top_id[t]] = top[t];
+            const Item &it = top_item[t];
+            if (it.slot_node >= 0) wide[top_id[it.slot_node]].ref[it.slot] = top_id[t];      // (parents come first in pop order)
+        }
+        for (const Sub &sb : subs) {
+            wide[top_id[sb.it.slot_node]].ref[sb.it.slot] = sb.base;
+            out.max_depth = std::max(out.max_depth, sb.deepest);
+        }
+        parallel_for((int)subs.size(), host_threads(), [&](int i) {
+            const Sub &sb = subs[i];
+            for (size_t j = 0; j < sb.W.size(); ++j) {
+                Wide w = sb.W[j];
+                for (int k = 0; k < 4; ++k) if (w.ref[k] >= 0 && w.ref[k] != FAST_EMPTY) w.ref[k] += sb.base;
+                wide[(size_t)sb.base + j] = w;
+            }
+        });
     }
 
     // Quantise: per node an origin p (float) and a power-of-two cell size 2^e per axis; child planes are bytes on that
