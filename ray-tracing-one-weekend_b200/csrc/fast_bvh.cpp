@@ -101,7 +101,11 @@ void parallel_for(int n, int threads, const F &f) {
     std::atomic<int> next(0);
     std::vector<std::thread> pool;
     auto work = [&] { for (int i = next++; i < n; i = next++) f(i); };
-    for (int t = 1; t < threads; ++t) pool.emplace_back(work);
+    try {
+        for (int t = 1; t < threads; ++t) pool.emplace_back(work);
+    } catch (...) {
+        // the system would not start another thread: the counter hands its share to the ones that run
+    }
     work();
     for (auto &t : pool) t.join();
 }
